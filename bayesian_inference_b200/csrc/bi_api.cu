@@ -1,0 +1,696 @@
+// bi_api.cu -- the C ABI of include/bi_b200.h: device image construction and kernel launches.  No torch, no CPU path.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <array>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/bi_b200.h"
+#include "chol_loglik.cuh"
+#include "common.cuh"
+#include "cov_assemble.cuh"
+#include "gp_predict.cuh"
+#include "setup_kernels.cuh"
+
+using namespace bi;
+
+namespace {
+
+struct GroupImg {
+    int N = 0, P = 0, Fg = 0, R = 0, nks = 0, ntn = 0, K0g = 0, pc_off = 0;
+    double* dXsT = nullptr;    // (P, d, N)
+    double* dEll = nullptr;    // (P, d)
+    double* dLinvF = nullptr;  // (P, ntn, 4, nks, 32)
+    double* dTg = nullptr;     // (Fg, K0g) row-major
+    double* dUs = nullptr;     // (Fg, Fg)
+    double* dMean = nullptr;   // (Fg)
+};
+
+}  // namespace
+
+struct bi_handle_s {
+    int device = 0, d = 0, G = 0, B = 0, F = 0, Fp = 0, nt = 0, Ptot = 0, K0 = 0, nks0 = 0, Nmax = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    std::vector<GroupImg> groups;
+    std::vector<void*> allocs;
+    PcDesc* dPcs = nullptr;
+    double *dMin = nullptr, *dMax = nullptr;
+    std::vector<double> hMin, hMax;
+    bool has_data = false, sigma_blockdiag = true;
+    double *dTrow = nullptr, *dTt = nullptr, *dTm = nullptr, *dE = nullptr, *dMeanMerged = nullptr, *dUblk = nullptr;
+    double *dSig = nullptr, *dYerr = nullptr, *dATiles = nullptr;
+    double a_ndiv = -1.0;
+    int *dObs = nullptr, *dTileOmin = nullptr, *dTileOmax = nullptr;
+    int *dKminDense = nullptr, *dImaxDense = nullptr, *dKminStruct = nullptr, *dImaxStruct = nullptr;
+    long long max_batch = 4096;
+    double *dTheta = nullptr, *dM = nullptr, *dV = nullptr, *dLogp = nullptr;
+    int* dInfo = nullptr;
+    unsigned long long* dCount = nullptr;
+    double* dWs = nullptr;
+    int chol_ctas = 0;
+    long long ws_stride = 0;
+    size_t chol_smem = 0, gp_smem = 0;
+    double* dOutScratch = nullptr;   // staging for *_host outputs (mean / cov / k)
+    size_t out_scratch_bytes = 0;
+    long long launches = 0;
+    size_t scratch_bytes = 0;
+    std::string err;
+};
+
+namespace {
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            if (h) h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                    \
+            return (int)e_;                                                                        \
+        }                                                                                          \
+    } while (0)
+
+int fail(bi_handle h, int code, const char* msg) {
+    if (h) h->err = msg;
+    return code;
+}
+
+template <typename T>
+int dalloc(bi_handle h, T** p, size_t n) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T));
+    if (e != cudaSuccess) {
+        h->err = std::string("cudaMalloc: ") + cudaGetErrorString(e);
+        return (int)e;
+    }
+    h->allocs.push_back(q);
+    h->scratch_bytes += n * sizeof(T);
+    *p = reinterpret_cast<T*>(q);
+    return 0;
+}
+
+template <typename T>
+int upload(bi_handle h, T** p, const T* src, size_t n) {
+    int rc = dalloc(h, p, n);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(*p, src, n * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+    return 0;
+}
+
+int ensure_out_scratch(bi_handle h, size_t bytes) {
+    if (bytes <= h->out_scratch_bytes) return 0;
+    if (h->dOutScratch) {
+        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaFree(h->dOutScratch));
+        h->dOutScratch = nullptr;
+        h->out_scratch_bytes = 0;
+    }
+    CK(cudaMalloc(&h->dOutScratch, bytes));
+    h->out_scratch_bytes = bytes;
+    return 0;
+}
+
+int build_a_tiles(bi_handle h, double n_div, cudaStream_t s) {
+    if (h->a_ndiv == n_div) return 0;
+    const int ntl = h->nt * (h->nt + 1) / 2;
+    build_a_tiles_kernel<<<ntl, 256, 0, s>>>(h->dSig, h->dYerr, h->dUblk, n_div, h->F, h->dATiles);
+    h->launches++;
+    CK(cudaGetLastError());
+    h->a_ndiv = n_div;
+    return 0;
+}
+
+int launch_gp(bi_handle h, const double* dTheta, long long W, double* dM, double* dV, cudaStream_t s) {
+    dim3 grid((unsigned)((W + GP_WT - 1) / GP_WT), (unsigned)h->Ptot);
+    gp_predict_kernel<true><<<grid, GP_THREADS, h->gp_smem, s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int launch_chol(bi_handle h, const double* dTheta, const double* dM, const double* dV, long long W, int mode,
+                double* dLogp, int* dInfo, cudaStream_t s) {
+    CholParams P;
+    P.F = h->F; P.Fp = h->Fp; P.nt = h->nt; P.K0 = h->K0; P.nks0 = h->nks0; P.Ptot = h->Ptot; P.d = h->d;
+    P.W = W; P.theta = dTheta; P.m = dM; P.v = dV; P.prior_min = h->dMin; P.prior_max = h->dMax;
+    P.Tt = h->dTt; P.Tm = h->dTm; P.e = h->dE; P.Atiles = h->dATiles; P.obs_id = h->dObs;
+    P.tile_omin = h->dTileOmin; P.tile_omax = h->dTileOmax;
+    P.kmin = (mode == BI_MODE_DENSE) ? h->dKminDense : h->dKminStruct;
+    P.imax = (mode == BI_MODE_DENSE) ? h->dImaxDense : h->dImaxStruct;
+    P.ws = h->dWs; P.ws_stride = h->ws_stride; P.logp = dLogp; P.info = dInfo; P.check_prior = 1;
+    const int grid = (int)std::min<long long>(W, h->chol_ctas);
+    chol_loglik_kernel<<<grid, CHOL_THREADS, h->chol_smem, s>>>(P);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bi_abi_version(void) { return BI_ABI_VERSION; }
+
+const char* bi_last_error(bi_handle h) { return h ? h->err.c_str() : "null handle"; }
+
+int64_t bi_query(bi_handle h, int what) {
+    if (!h) return -1;
+    switch (what) {
+        case 0: return h->F;
+        case 1: return h->Ptot;
+        case 2: return h->d;
+        case 3: return h->G;
+        case 4: return h->sm_count;
+        case 5: return h->chol_ctas;
+        case 6: return (int64_t)h->scratch_bytes;
+        case 7: return h->launches;
+        default: return -1;
+    }
+}
+
+int bi_sync(bi_handle h) {
+    if (!h) return BI_E_ARG;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+void bi_destroy(bi_handle h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (void* p : h->allocs) cudaFree(p);
+    if (h->dOutScratch) cudaFree(h->dOutScratch);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+int bi_create(const bi_desc* D, bi_handle* out) {
+    if (!D || !out) return BI_E_ARG;
+    *out = nullptr;
+    if (D->abi_version != BI_ABI_VERSION) return BI_E_ARG;
+    if (D->d <= 0 || D->n_groups <= 0 || D->n_blocks <= 0 || D->n_features <= 0 || !D->groups || !D->blocks ||
+        !D->prior_min || !D->prior_max)
+        return BI_E_ARG;
+    bi_handle h = new bi_handle_s();
+    auto bail = [&](int rc) {
+        std::fprintf(stderr, "bi_create failed (%d): %s\n", rc, h->err.c_str());
+        bi_destroy(h);
+        return rc;
+    };
+#define TRY(x)                      \
+    do {                            \
+        int rc_ = (x);              \
+        if (rc_) return bail(rc_);  \
+    } while (0)
+#define CKB(call)                                                              \
+    do {                                                                       \
+        cudaError_t e_ = (call);                                               \
+        if (e_ != cudaSuccess) {                                               \
+            h->err = std::string(#call) + ": " + cudaGetErrorString(e_);       \
+            return bail((int)e_);                                              \
+        }                                                                      \
+    } while (0)
+
+    h->device = D->device;
+    CKB(cudaSetDevice(h->device));
+    cudaDeviceProp prop;
+    CKB(cudaGetDeviceProperties(&prop, h->device));
+    if (prop.major < 10) {
+        h->err = "this library is built for sm_100a (B200) only";
+        return bail(BI_E_UNSUPPORTED);
+    }
+    h->sm_count = prop.multiProcessorCount;
+    CKB(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    h->d = D->d; h->G = D->n_groups; h->B = D->n_blocks; h->F = D->n_features;
+    h->nt = (h->F + 31) / 32; h->Fp = h->nt * 32;
+    if (D->max_batch > 0) h->max_batch = D->max_batch;
+    const int d = h->d, F = h->F, Fp = h->Fp, nt = h->nt;
+    h->hMin.assign(D->prior_min, D->prior_min + d);
+    h->hMax.assign(D->prior_max, D->prior_max + d);
+    TRY(upload(h, &h->dMin, D->prior_min, (size_t)d));
+    TRY(upload(h, &h->dMax, D->prior_max, (size_t)d));
+
+    // ---- per-group images -------------------------------------------------------------------------------------
+    h->groups.resize(h->G);
+    int pc_off = 0;
+    for (int gi = 0; gi < h->G; ++gi) {
+        const bi_group_desc& g = D->groups[gi];
+        GroupImg& I = h->groups[gi];
+        if (g.n_design <= 0 || g.n_pc <= 0 || g.n_features <= 0 || g.n_rest < 0 || !g.X || !g.kind || !g.ell ||
+            !g.constant || !g.noise || !g.alpha || !g.L || !g.S || !g.scale || !g.mean ||
+            (g.n_rest > 0 && (!g.S_rest || !g.ev_rest))) {
+            h->err = "group descriptor has a null or non-positive field";
+            return bail(BI_E_ARG);
+        }
+        I.N = g.n_design; I.P = g.n_pc; I.Fg = g.n_features; I.R = g.n_rest;
+        I.nks = (I.N + 3) / 4; I.ntn = (I.N + 1 + 31) / 32; I.K0g = ((I.P + 3) / 4) * 4; I.pc_off = pc_off;
+        pc_off += I.P;
+        h->Nmax = std::max(h->Nmax, I.N);
+        const int N = I.N, Pg = I.P, Fg = I.Fg;
+        for (int p = 0; p < Pg; ++p)
+            if (g.kind[p] < 0 || g.kind[p] > 3) {
+                h->err = "unknown kernel kind";
+                return bail(BI_E_ARG);
+            }
+        // X / ell, transposed (sklearn divides both operands by length_scale before cdist, kernels.py:1688)
+        std::vector<double> xs((size_t)Pg * d * N);
+        for (int p = 0; p < Pg; ++p)
+            for (int k = 0; k < d; ++k)
+                for (int j = 0; j < N; ++j) xs[((size_t)p * d + k) * N + j] = g.X[(size_t)j * d + k] / g.ell[(size_t)p * d + k];
+        TRY(upload(h, &I.dXsT, xs.data(), xs.size()));
+        TRY(upload(h, &I.dEll, g.ell, (size_t)Pg * d));
+        // L^-1 (+ alpha row), operand-fragment-major
+        double *dL = nullptr, *dX = nullptr, *dAlpha = nullptr;
+        CKB(cudaMalloc(&dL, (size_t)Pg * N * N * sizeof(double)));
+        CKB(cudaMalloc(&dX, (size_t)Pg * N * N * sizeof(double)));
+        CKB(cudaMalloc(&dAlpha, (size_t)Pg * N * sizeof(double)));
+        CKB(cudaMemcpyAsync(dL, g.L, (size_t)Pg * N * N * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        CKB(cudaMemcpyAsync(dAlpha, g.alpha, (size_t)Pg * N * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        CKB(cudaMemsetAsync(dX, 0, (size_t)Pg * N * N * sizeof(double), h->stream));
+        const size_t inv_smem = (size_t)N * 32 * sizeof(double);
+        if (inv_smem > 227 * 1024) {
+            h->err = "n_design too large for the triangular-inverse setup kernel (max 908)";
+            return bail(BI_E_UNSUPPORTED);
+        }
+        CKB(cudaFuncSetAttribute(tri_invert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)inv_smem));
+        tri_invert_kernel<<<dim3((N + 31) / 32, Pg), 32, inv_smem, h->stream>>>(dL, dX, N);
+        CKB(cudaGetLastError());
+        const size_t per_pc = (size_t)I.ntn * 4 * I.nks * 32;
+        TRY(dalloc(h, &I.dLinvF, per_pc * Pg));
+        pack_linv_kernel<<<dim3((unsigned)((per_pc + 255) / 256), Pg), 256, 0, h->stream>>>(dX, dAlpha, I.dLinvF, N, I.nks, I.ntn);
+        CKB(cudaGetLastError());
+        // T_g = scale * S^T (Fg, K0g), unexplained covariance, scaler mean
+        std::vector<double> tg((size_t)Fg * I.K0g, 0.0);
+        for (int r = 0; r < Fg; ++r)
+            for (int q = 0; q < Pg; ++q) tg[(size_t)r * I.K0g + q] = g.scale[r] * g.S[(size_t)q * Fg + r];
+        TRY(upload(h, &I.dTg, tg.data(), tg.size()));
+        TRY(upload(h, &I.dMean, g.mean, (size_t)Fg));
+        TRY(dalloc(h, &I.dUs, (size_t)Fg * Fg));
+        if (I.R > 0) {
+            double *dSr = nullptr, *dEv = nullptr, *dSc = nullptr;
+            CKB(cudaMalloc(&dSr, (size_t)I.R * Fg * sizeof(double)));
+            CKB(cudaMalloc(&dEv, (size_t)I.R * sizeof(double)));
+            CKB(cudaMalloc(&dSc, (size_t)Fg * sizeof(double)));
+            CKB(cudaMemcpyAsync(dSr, g.S_rest, (size_t)I.R * Fg * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            CKB(cudaMemcpyAsync(dEv, g.ev_rest, (size_t)I.R * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            CKB(cudaMemcpyAsync(dSc, g.scale, (size_t)Fg * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            unexplained_kernel<<<dim3((Fg + 31) / 32, (Fg + 7) / 8), 256, 0, h->stream>>>(dSr, dEv, dSc, I.dUs, Fg, I.R);
+            CKB(cudaGetLastError());
+            CKB(cudaStreamSynchronize(h->stream));
+            cudaFree(dSr); cudaFree(dEv); cudaFree(dSc);
+        } else {
+            CKB(cudaMemsetAsync(I.dUs, 0, (size_t)Fg * Fg * sizeof(double), h->stream));
+        }
+        CKB(cudaStreamSynchronize(h->stream));
+        cudaFree(dL); cudaFree(dX); cudaFree(dAlpha);
+    }
+    h->Ptot = pc_off;
+    h->K0 = ((h->Ptot + 3) / 4) * 4;
+    h->nks0 = h->K0 / 4;
+
+    // ---- PC descriptors ---------------------------------------------------------------------------------------
+    {
+        std::vector<PcDesc> pcs((size_t)h->Ptot);
+        for (int gi = 0; gi < h->G; ++gi) {
+            const bi_group_desc& g = D->groups[gi];
+            const GroupImg& I = h->groups[gi];
+            for (int p = 0; p < I.P; ++p) {
+                PcDesc& pc = pcs[(size_t)I.pc_off + p];
+                pc.XsT = I.dXsT + (size_t)p * d * I.N;
+                pc.ell = I.dEll + (size_t)p * d;
+                pc.LinvF = I.dLinvF + (size_t)p * I.ntn * 4 * I.nks * 32;
+                pc.N = I.N; pc.nks = I.nks; pc.ntn = I.ntn; pc.kind = g.kind[p];
+                pc.cst = g.constant[p];
+                pc.diag = (1.0 + g.constant[p]) + g.noise[p];
+                pc.group = gi; pc.local = p;
+            }
+        }
+        TRY(upload(h, &h->dPcs, pcs.data(), pcs.size()));
+    }
+
+    // ---- merged layout (emulation.py:346-406) ---------------------------------------------------------------
+    std::vector<int> row_group((size_t)F, -1), row_in((size_t)F, -1), obs((size_t)Fp, 0);
+    {
+        std::vector<std::array<long long, 4>> blocks((size_t)h->B);
+        for (int b = 0; b < h->B; ++b)
+            for (int k = 0; k < 4; ++k) blocks[b][k] = D->blocks[(size_t)b * 4 + k];
+        std::sort(blocks.begin(), blocks.end(), [](const auto& a, const auto& b) { return a[1] < b[1]; });
+        for (int b = 0; b < h->B; ++b) {
+            const long long gi = blocks[b][0], so = blocks[b][1], si = blocks[b][2], ln = blocks[b][3];
+            if (gi < 0 || gi >= h->G || ln <= 0 || so < 0 || so + ln > F || si < 0 || si + ln > h->groups[gi].Fg) {
+                h->err = "observable block outside its matrix";
+                return bail(BI_E_ARG);
+            }
+            for (long long r = 0; r < ln; ++r) {
+                if (row_group[so + r] != -1) {
+                    h->err = "observable blocks overlap";
+                    return bail(BI_E_ARG);
+                }
+                row_group[so + r] = (int)gi; row_in[so + r] = (int)(si + r); obs[so + r] = b;
+            }
+        }
+        for (int r = 0; r < F; ++r)
+            if (row_group[r] < 0) {
+                h->err = "observable blocks do not cover the merged feature axis";
+                return bail(BI_E_ARG);
+            }
+        for (int r = F; r < Fp; ++r) obs[r] = h->B + (r - F);
+        TRY(dalloc(h, &h->dUblk, (size_t)F * F));
+        CKB(cudaMemsetAsync(h->dUblk, 0, (size_t)F * F * sizeof(double), h->stream));
+        for (int b = 0; b < h->B; ++b) {
+            const long long gi = blocks[b][0], so = blocks[b][1], si = blocks[b][2], ln = blocks[b][3];
+            const GroupImg& I = h->groups[gi];
+            CKB(cudaMemcpy2DAsync(h->dUblk + (size_t)so * F + so, (size_t)F * sizeof(double),
+                                  I.dUs + (size_t)si * I.Fg + si, (size_t)I.Fg * sizeof(double),
+                                  (size_t)ln * sizeof(double), (size_t)ln, cudaMemcpyDeviceToDevice, h->stream));
+        }
+    }
+    {
+        const int K0 = h->K0, nks0 = h->nks0;
+        std::vector<double> trow((size_t)F * K0, 0.0), tt((size_t)K0 * Fp, 0.0), tm((size_t)nt * 4 * nks0 * 32, 0.0),
+            mean((size_t)F, 0.0), ev((size_t)Fp, 0.0);
+        for (int r = 0; r < F; ++r) {
+            const int gi = row_group[r], ri = row_in[r];
+            const bi_group_desc& g = D->groups[gi];
+            const GroupImg& I = h->groups[gi];
+            for (int p = 0; p < I.P; ++p) {
+                const double tv = g.scale[ri] * g.S[(size_t)p * I.Fg + ri];
+                const int q = I.pc_off + p;
+                trow[(size_t)r * K0 + q] = tv;
+                tt[(size_t)q * Fp + r] = tv;
+                tm[(size_t)(r / 32) * 4 * nks0 * 32 + of_index(r % 32, q, nks0)] = tv;
+            }
+            mean[r] = g.mean[ri];
+            if (D->y) ev[r] = g.mean[ri] - D->y[r];
+        }
+        TRY(upload(h, &h->dTrow, trow.data(), trow.size()));
+        TRY(upload(h, &h->dTt, tt.data(), tt.size()));
+        TRY(upload(h, &h->dTm, tm.data(), tm.size()));
+        TRY(upload(h, &h->dMeanMerged, mean.data(), mean.size()));
+        TRY(upload(h, &h->dE, ev.data(), ev.size()));
+        CKB(cudaStreamSynchronize(h->stream));
+    }
+    {
+        std::vector<int> omin((size_t)nt), omax((size_t)nt), kminD((size_t)nt, 0), imaxD((size_t)nt, nt - 1),
+            kminS((size_t)nt), imaxS((size_t)nt);
+        for (int i = 0; i < nt; ++i) { omin[i] = obs[(size_t)i * 32]; omax[i] = obs[(size_t)i * 32 + 31]; }
+        for (int i = 0; i < nt; ++i) {
+            int k = 0;
+            while (omax[k] < omin[i]) ++k;
+            kminS[i] = k;
+        }
+        for (int j = 0; j < nt; ++j) {
+            int i = j;
+            while (i + 1 < nt && kminS[i + 1] <= j) ++i;
+            imaxS[j] = i;
+        }
+        TRY(upload(h, &h->dObs, obs.data(), obs.size()));
+        TRY(upload(h, &h->dTileOmin, omin.data(), omin.size()));
+        TRY(upload(h, &h->dTileOmax, omax.data(), omax.size()));
+        TRY(upload(h, &h->dKminDense, kminD.data(), kminD.size()));
+        TRY(upload(h, &h->dImaxDense, imaxD.data(), imaxD.size()));
+        TRY(upload(h, &h->dKminStruct, kminS.data(), kminS.size()));
+        TRY(upload(h, &h->dImaxStruct, imaxS.data(), imaxS.size()));
+        CKB(cudaStreamSynchronize(h->stream));
+    }
+
+    // ---- experimental data ------------------------------------------------------------------------------------
+    h->has_data = (D->y != nullptr) && (D->y_err != nullptr || D->sigma_exp != nullptr);
+    if (h->has_data) {
+        if (D->sigma_exp) {
+            TRY(upload(h, &h->dSig, D->sigma_exp, (size_t)F * F));
+            for (int r = 0; r < F && h->sigma_blockdiag; ++r)
+                for (int c = 0; c < F; ++c)
+                    if (obs[r] != obs[c] && D->sigma_exp[(size_t)r * F + c] != 0.0) { h->sigma_blockdiag = false; break; }
+        } else {
+            TRY(upload(h, &h->dYerr, D->y_err, (size_t)F));
+        }
+        TRY(dalloc(h, &h->dATiles, (size_t)nt * (nt + 1) / 2 * TILE_ELEMS));
+        CKB(cudaStreamSynchronize(h->stream));
+    }
+
+    // ---- per-call scratch ---------------------------------------------------------------------------------------
+    const long long mb = h->max_batch;
+    TRY(dalloc(h, &h->dTheta, (size_t)mb * d));
+    TRY(dalloc(h, &h->dM, (size_t)mb * h->Ptot));
+    TRY(dalloc(h, &h->dV, (size_t)mb * h->Ptot));
+    TRY(dalloc(h, &h->dLogp, (size_t)mb));
+    TRY(dalloc(h, &h->dInfo, (size_t)mb));
+    TRY(dalloc(h, &h->dCount, (size_t)1));
+
+    h->gp_smem = gp_smem_bytes(d, h->Nmax);
+    if (h->gp_smem > 227 * 1024) {
+        h->err = "n_design too large for the GP kernel's shared-memory operand tile";
+        return bail(BI_E_UNSUPPORTED);
+    }
+    CKB(cudaFuncSetAttribute(gp_predict_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
+    CKB(cudaFuncSetAttribute(gp_predict_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
+    {
+        const size_t cs = (size_t)(2 * 32 * (std::max(h->K0, 4) + 1) + std::max(h->K0, 4)) * sizeof(double);
+        CKB(cudaFuncSetAttribute(cov_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(cs, 48 * 1024)));
+    }
+    if (h->has_data) {
+        h->chol_smem = chol_smem_bytes(Fp, h->K0);
+        CKB(cudaFuncSetAttribute(chol_loglik_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chol_smem));
+        int occ = 0;
+        CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_loglik_kernel, CHOL_THREADS, h->chol_smem));
+        if (occ < 1) {
+            h->err = "Cholesky kernel does not fit on an SM";
+            return bail(BI_E_UNSUPPORTED);
+        }
+        h->chol_ctas = h->sm_count * occ;
+        h->ws_stride = chol_ws_doubles(nt);
+        TRY(dalloc(h, &h->dWs, (size_t)h->chol_ctas * h->ws_stride));
+    }
+    CKB(cudaStreamSynchronize(h->stream));
+    *out = h;
+    return 0;
+#undef TRY
+#undef CKB
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+int bi_kernel_vectors(bi_handle h, int group, const double* theta, int64_t W, double* k_out, void* stream) {
+    if (!h || !theta || !k_out || W < 0 || group < 0 || group >= h->G) return fail(h, BI_E_ARG, "bad argument");
+    if (W == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    const GroupImg& I = h->groups[group];
+    dim3 grid((unsigned)((W + GP_WT - 1) / GP_WT), (unsigned)I.P);
+    gp_predict_kernel<false><<<grid, GP_THREADS, h->gp_smem, s>>>(h->dPcs, I.pc_off, h->d, theta, W, k_out, I.P, nullptr,
+                                                                  nullptr, h->Ptot);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int bi_kernel_vectors_host(bi_handle h, int group, const double* theta, int64_t W, double* k_out) {
+    if (!h || !theta || !k_out || W < 0 || group < 0 || group >= h->G) return fail(h, BI_E_ARG, "bad argument");
+    CK(cudaSetDevice(h->device));
+    const GroupImg& I = h->groups[group];
+    const size_t per = (size_t)I.P * I.N;
+    const long long chunk = std::min<long long>(h->max_batch, std::max<long long>(1, (256ll << 20) / (long long)(per * 8)));
+    int rc = ensure_out_scratch(h, (size_t)chunk * per * 8);
+    if (rc) return rc;
+    for (long long w0 = 0; w0 < W; w0 += chunk) {
+        const long long wb = std::min<long long>(chunk, W - w0);
+        CK(cudaMemcpyAsync(h->dTheta, theta + w0 * h->d, (size_t)wb * h->d * 8, cudaMemcpyHostToDevice, h->stream));
+        rc = bi_kernel_vectors(h, group, h->dTheta, wb, h->dOutScratch, h->stream);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(k_out + (size_t)w0 * per, h->dOutScratch, (size_t)wb * per * 8, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return 0;
+}
+
+int bi_predict_pc(bi_handle h, const double* theta, int64_t W, double* m_out, double* v_out, void* stream) {
+    if (!h || !theta || !m_out || !v_out || W < 0) return fail(h, BI_E_ARG, "bad argument");
+    if (W == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    return launch_gp(h, theta, W, m_out, v_out, stream ? (cudaStream_t)stream : h->stream);
+}
+
+int bi_predict_pc_host(bi_handle h, const double* theta, int64_t W, double* m_out, double* v_out) {
+    if (!h || !theta || !m_out || !v_out || W < 0) return fail(h, BI_E_ARG, "bad argument");
+    CK(cudaSetDevice(h->device));
+    for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
+        const long long wb = std::min<long long>(h->max_batch, W - w0);
+        CK(cudaMemcpyAsync(h->dTheta, theta + w0 * h->d, (size_t)wb * h->d * 8, cudaMemcpyHostToDevice, h->stream));
+        int rc = launch_gp(h, h->dTheta, wb, h->dM, h->dV, h->stream);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(m_out + w0 * h->Ptot, h->dM, (size_t)wb * h->Ptot * 8, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaMemcpyAsync(v_out + w0 * h->Ptot, h->dV, (size_t)wb * h->Ptot * 8, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return 0;
+}
+
+static int predict_any(bi_handle h, int group, const double* theta, int64_t W, double n_div, double* mean_out,
+                       double* cov_out, cudaStream_t s, double* dM, double* dV) {
+    // theta, outputs: device pointers; dM/dV: (W, Ptot) scratch
+    int rc = launch_gp(h, theta, W, dM, dV, s);
+    if (rc) return rc;
+    CovParams P;
+    if (group < 0) {
+        P.Fo = h->F; P.K0 = h->K0; P.voff = 0; P.nq = h->Ptot; P.Trow = h->dTrow; P.Uc = h->dUblk;
+        P.mu = h->dMeanMerged; P.obs = h->dObs;
+    } else {
+        const GroupImg& I = h->groups[group];
+        P.Fo = I.Fg; P.K0 = I.K0g; P.voff = I.pc_off; P.nq = I.P; P.Trow = I.dTg; P.Uc = I.dUs; P.mu = I.dMean;
+        P.obs = nullptr;
+    }
+    P.Ptot = h->Ptot; P.m = dM; P.v = dV; P.n_div = n_div; P.mean_out = mean_out; P.cov_out = cov_out; P.W = W;
+    if (mean_out) {
+        const long long n = W * P.Fo;
+        mean_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(P);
+        h->launches++;
+        CK(cudaGetLastError());
+    }
+    if (cov_out) {
+        const size_t smem = (size_t)(2 * 32 * (P.K0 + 1) + P.K0) * sizeof(double);
+        cov_assemble_kernel<<<dim3((P.Fo + 31) / 32, (unsigned)W), 256, smem, s>>>(P);
+        h->launches++;
+        CK(cudaGetLastError());
+    }
+    return 0;
+}
+
+static int predict_dev(bi_handle h, int group, const double* theta, int64_t W, double n_div, double* mean_out,
+                       double* cov_out, void* stream) {
+    if (!h || !theta || W < 0 || group >= h->G || !(n_div > 0.0)) return fail(h, BI_E_ARG, "bad argument");
+    if (W == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    const int Fo = group < 0 ? h->F : h->groups[group].Fg;
+    for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
+        const long long wb = std::min<long long>(h->max_batch, W - w0);
+        int rc = predict_any(h, group, theta + w0 * h->d, wb, n_div, mean_out ? mean_out + w0 * Fo : nullptr,
+                             cov_out ? cov_out + (size_t)w0 * Fo * Fo : nullptr, s, h->dM, h->dV);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+static int predict_host(bi_handle h, int group, const double* theta, int64_t W, double n_div, double* mean_out,
+                        double* cov_out) {
+    if (!h || !theta || W < 0 || group >= h->G || !(n_div > 0.0)) return fail(h, BI_E_ARG, "bad argument");
+    CK(cudaSetDevice(h->device));
+    const int Fo = group < 0 ? h->F : h->groups[group].Fg;
+    const size_t per = (size_t)Fo * (cov_out ? (size_t)Fo + 1 : 1) * 8;
+    const long long chunk = std::min<long long>(h->max_batch, std::max<long long>(1, (long long)((512ull << 20) / per)));
+    int rc = ensure_out_scratch(h, (size_t)chunk * per);
+    if (rc) return rc;
+    double* dMean = h->dOutScratch;
+    double* dCov = cov_out ? h->dOutScratch + (size_t)chunk * Fo : nullptr;
+    for (long long w0 = 0; w0 < W; w0 += chunk) {
+        const long long wb = std::min<long long>(chunk, W - w0);
+        CK(cudaMemcpyAsync(h->dTheta, theta + w0 * h->d, (size_t)wb * h->d * 8, cudaMemcpyHostToDevice, h->stream));
+        rc = predict_any(h, group, h->dTheta, wb, n_div, dMean, dCov, h->stream, h->dM, h->dV);
+        if (rc) return rc;
+        if (mean_out) CK(cudaMemcpyAsync(mean_out + w0 * Fo, dMean, (size_t)wb * Fo * 8, cudaMemcpyDeviceToHost, h->stream));
+        if (cov_out)
+            CK(cudaMemcpyAsync(cov_out + (size_t)w0 * Fo * Fo, dCov, (size_t)wb * Fo * Fo * 8, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return 0;
+}
+
+int bi_predict_group(bi_handle h, int group, const double* theta, int64_t W, double n_div, double* mean_out,
+                     double* cov_out, void* stream) {
+    if (group < 0) return fail(h, BI_E_ARG, "bad group");
+    return predict_dev(h, group, theta, W, n_div, mean_out, cov_out, stream);
+}
+int bi_predict_group_host(bi_handle h, int group, const double* theta, int64_t W, double n_div, double* mean_out,
+                          double* cov_out) {
+    if (group < 0) return fail(h, BI_E_ARG, "bad group");
+    return predict_host(h, group, theta, W, n_div, mean_out, cov_out);
+}
+int bi_predict(bi_handle h, const double* theta, int64_t W, double n_div, double* mean_out, double* cov_out, void* stream) {
+    return predict_dev(h, -1, theta, W, n_div, mean_out, cov_out, stream);
+}
+int bi_predict_host(bi_handle h, const double* theta, int64_t W, double n_div, double* mean_out, double* cov_out) {
+    return predict_host(h, -1, theta, W, n_div, mean_out, cov_out);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+static int check_lp(bi_handle h, const double* theta, int64_t W, int mode, double* logp_out) {
+    if (!h || !theta || !logp_out || W < 0) return fail(h, BI_E_ARG, "bad argument");
+    if (!h->has_data) return fail(h, BI_E_STATE, "handle was created without experimental data");
+    if (mode != BI_MODE_DENSE && mode != BI_MODE_STRUCTURED) return fail(h, BI_E_UNSUPPORTED, "mode not implemented");
+    if (mode == BI_MODE_STRUCTURED && !h->sigma_blockdiag)
+        return fail(h, BI_E_STRUCTURE, "Sigma_exp couples observable blocks: structured mode is not valid");
+    return 0;
+}
+
+int bi_log_posterior(bi_handle h, const double* theta, int64_t W, double n_div, int mode, double* logp_out,
+                     int32_t* info_out, void* stream) {
+    int rc = check_lp(h, theta, W, mode, logp_out);
+    if (rc) return rc;
+    if (W == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    if (!(n_div > 0.0)) {
+        // rows inside the prior box in this call (log_posterior.py:67 -> emulation.py:493); needs one readback
+        CK(cudaMemsetAsync(h->dCount, 0, sizeof(unsigned long long), s));
+        count_inside_kernel<<<(unsigned)((W + 255) / 256), 256, 0, s>>>(theta, W, h->d, h->dMin, h->dMax, h->dCount);
+        h->launches++;
+        unsigned long long cnt = 0;
+        CK(cudaMemcpyAsync(&cnt, h->dCount, sizeof(cnt), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        n_div = cnt > 0 ? (double)cnt : 1.0;
+    }
+    rc = build_a_tiles(h, n_div, s);
+    if (rc) return rc;
+    for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
+        const long long wb = std::min<long long>(h->max_batch, W - w0);
+        rc = launch_gp(h, theta + w0 * h->d, wb, h->dM, h->dV, s);
+        if (rc) return rc;
+        rc = launch_chol(h, theta + w0 * h->d, h->dM, h->dV, wb, mode, logp_out + w0, info_out ? info_out + w0 : nullptr, s);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int bi_log_posterior_host(bi_handle h, const double* theta, int64_t W, double n_div, int mode, double* logp_out,
+                          int32_t* info_out) {
+    int rc = check_lp(h, theta, W, mode, logp_out);
+    if (rc) return rc;
+    if (W == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    if (!(n_div > 0.0)) {
+        long long cnt = 0;
+        for (long long w = 0; w < W; ++w) {
+            bool in = true;
+            for (int k = 0; k < h->d; ++k) {
+                const double x = theta[w * h->d + k];
+                if (!(x > h->hMin[k] && x < h->hMax[k])) in = false;
+            }
+            cnt += in;
+        }
+        n_div = cnt > 0 ? (double)cnt : 1.0;
+    }
+    rc = build_a_tiles(h, n_div, h->stream);
+    if (rc) return rc;
+    for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
+        const long long wb = std::min<long long>(h->max_batch, W - w0);
+        CK(cudaMemcpyAsync(h->dTheta, theta + w0 * h->d, (size_t)wb * h->d * 8, cudaMemcpyHostToDevice, h->stream));
+        rc = launch_gp(h, h->dTheta, wb, h->dM, h->dV, h->stream);
+        if (rc) return rc;
+        rc = launch_chol(h, h->dTheta, h->dM, h->dV, wb, mode, h->dLogp, h->dInfo, h->stream);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(logp_out + w0, h->dLogp, (size_t)wb * 8, cudaMemcpyDeviceToHost, h->stream));
+        if (info_out) CK(cudaMemcpyAsync(info_out + w0, h->dInfo, (size_t)wb * 4, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return 0;
+}
+
+int bi_loglikelihood_host(bi_handle h, const double*, const double*, int64_t, int32_t, double*, int32_t*) {
+    return fail(h, BI_E_UNSUPPORTED, "bi_loglikelihood_host: not implemented yet");
+}
+
+}  // extern "C"

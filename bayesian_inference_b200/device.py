@@ -1,0 +1,222 @@
+"""``DeviceEmulator``: the emulator image resident in one GPU's HBM, driven through the C ABI (include/bi_b200.h).
+
+This is the host-side owner of a ``bi_handle``.  It is what ``log_posterior.initialize_pool_variables`` builds once
+(the reference pickles the emulators to every pool worker instead, mcmc.py:77-78) and what ``emulation.predict`` /
+``log_posterior.log_posterior`` call.  numpy arrays go through the ``*_host`` entry points (copy in, run, copy out);
+torch CUDA tensors go through the device-pointer entry points on torch's current stream and never leave the GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+
+from . import _lib
+from .image import EmulatorImage
+
+
+def _f64(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class DeviceError(RuntimeError):
+    pass
+
+
+class DeviceEmulator:
+    def __init__(self, image: EmulatorImage, device: int = 0, max_batch: int = 0):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        self.image = image
+        self.device = int(device)
+        self.d = image.d
+        self.n_features = image.n_features
+        self.group_names = image.group_names
+        self.n_pc = [g.n_pc for g in image.groups]
+        self.n_pc_total = sum(self.n_pc)
+        keep = []   # host arrays must outlive bi_create
+
+        def hold(a, dtype=np.float64):
+            a = np.ascontiguousarray(a, dtype=dtype)
+            keep.append(a)
+            return a.ctypes.data_as(C.c_void_p)
+
+        garr = (_lib.GroupDesc * len(image.groups))()
+        for i, g in enumerate(image.groups):
+            gd = garr[i]
+            gd.n_design, gd.n_pc, gd.n_features, gd.n_rest = g.n_design, g.n_pc, g.n_features, int(g.S_rest.shape[0])
+            gd.X, gd.kind, gd.ell = hold(g.X), hold(g.kind, np.int32), hold(g.ell)
+            gd.constant, gd.noise, gd.alpha, gd.L = hold(g.const), hold(g.noise), hold(g.alpha), hold(g.L)
+            gd.S, gd.scale, gd.mean = hold(g.S), hold(g.scale), hold(g.mean)
+            if g.S_rest.shape[0] > 0:
+                gd.S_rest, gd.ev_rest = hold(g.S_rest), hold(g.ev_rest)
+        desc = _lib.Desc()
+        desc.abi_version = 1
+        desc.device = self.device
+        desc.d = image.d
+        desc.n_groups = len(image.groups)
+        desc.n_blocks = int(image.blocks.shape[0])
+        desc.n_features = image.n_features
+        desc.groups = garr
+        desc.blocks = hold(image.blocks, np.int64)
+        desc.prior_min, desc.prior_max = hold(image.min), hold(image.max)
+        self.has_data = image.y is not None and (image.y_err is not None or image.sigma_exp is not None)
+        if image.y is not None:
+            desc.y = hold(image.y)
+        if image.sigma_exp is not None:
+            desc.sigma_exp = hold(image.sigma_exp)
+        elif image.y_err is not None:
+            desc.y_err = hold(image.y_err)
+        desc.max_batch = int(max_batch)
+        rc = self._lib.bi_create(C.byref(desc), C.byref(self._h))
+        if rc != 0 or not self._h:
+            self._h = C.c_void_p()
+            raise DeviceError(f"bi_create failed with code {rc} (see stderr); there is no CPU fallback")
+
+    # ---- lifetime -------------------------------------------------------------------------------------------
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.bi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc: int, what: str) -> None:
+        if rc != 0:
+            msg = self._lib.bi_last_error(self._h)
+            raise DeviceError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+    def query(self, what: int) -> int:
+        return int(self._lib.bi_query(self._h, what))
+
+    @property
+    def launches(self) -> int:
+        """Kernels launched by this handle since creation."""
+        return self.query(7)
+
+    def sync(self) -> None:
+        self._check(self._lib.bi_sync(self._h), "bi_sync")
+
+    def _theta(self, theta) -> np.ndarray:
+        th = np.asarray(theta, dtype=np.float64)
+        if th.ndim == 1:
+            th = th[None, :]
+        if th.ndim != 2 or th.shape[1] != self.d:
+            raise ValueError(f"theta has shape {th.shape}, expected (W, {self.d})")
+        return np.ascontiguousarray(th)
+
+    # ---- numpy (host) API -----------------------------------------------------------------------------------
+    def kernel_vectors(self, group: int, theta) -> np.ndarray:
+        th = self._theta(theta)
+        g = self.image.groups[group]
+        out = np.empty((th.shape[0], g.n_pc, g.n_design))
+        self._check(self._lib.bi_kernel_vectors_host(self._h, group, _ptr(th), th.shape[0], _ptr(out)), "bi_kernel_vectors")
+        return out
+
+    def predict_pc(self, theta) -> tuple[np.ndarray, np.ndarray]:
+        th = self._theta(theta)
+        m = np.empty((th.shape[0], self.n_pc_total))
+        v = np.empty_like(m)
+        self._check(self._lib.bi_predict_pc_host(self._h, _ptr(th), th.shape[0], _ptr(m), _ptr(v)), "bi_predict_pc")
+        return m, v
+
+    def predict_group(self, group: int, theta, n_div: Optional[float] = None, want_cov: bool = True):
+        th = self._theta(theta)
+        W, Fg = th.shape[0], self.image.groups[group].n_features
+        nd = float(W if n_div is None else n_div)
+        mean = np.empty((W, Fg))
+        cov = np.empty((W, Fg, Fg)) if want_cov else None
+        if W:
+            self._check(self._lib.bi_predict_group_host(self._h, group, _ptr(th), W, nd, _ptr(mean), _ptr(cov)),
+                        "bi_predict_group")
+        return mean, cov
+
+    def predict(self, theta, n_div: Optional[float] = None, want_cov: bool = True):
+        th = self._theta(theta)
+        W, F = th.shape[0], self.n_features
+        nd = float(W if n_div is None else n_div)
+        mean = np.empty((W, F))
+        cov = np.empty((W, F, F)) if want_cov else None
+        if W:
+            self._check(self._lib.bi_predict_host(self._h, _ptr(th), W, nd, _ptr(mean), _ptr(cov)), "bi_predict")
+        return mean, cov
+
+    def log_posterior(self, theta, n_div: Optional[float] = 1.0, mode: str = "dense", return_info: bool = False):
+        """``n_div=None`` -> rows inside the prior box in this call (a batched reference call)."""
+        th = self._theta(theta)
+        W = th.shape[0]
+        out = np.empty(W)
+        info = np.zeros(W, dtype=np.int32)
+        if W:
+            nd = -1.0 if n_div is None else float(n_div)
+            self._check(self._lib.bi_log_posterior_host(self._h, _ptr(th), W, nd, _lib.MODE[mode], _ptr(out), _ptr(info)),
+                        "bi_log_posterior")
+        return (out, info) if return_info else out
+
+    def loglikelihood(self, dy, cov, return_info: bool = False):
+        dy = _f64(dy)
+        cov = _f64(cov)
+        if dy.ndim == 1:
+            dy, cov = dy[None], cov[None]
+        n, Fd = dy.shape
+        if cov.shape != (n, Fd, Fd):
+            raise ValueError(f"cov has shape {cov.shape}, expected {(n, Fd, Fd)}")
+        out = np.empty(n)
+        info = np.zeros(n, dtype=np.int32)
+        self._check(self._lib.bi_loglikelihood_host(self._h, _ptr(dy), _ptr(cov), n, Fd, _ptr(out), _ptr(info)),
+                    "bi_loglikelihood")
+        return (out, info) if return_info else out
+
+    # ---- torch (device-resident) API --------------------------------------------------------------------------
+    def log_posterior_tensor(self, theta, n_div: float = 1.0, mode: str = "dense", out=None, info=None):
+        """theta: torch.float64 CUDA tensor (W, d) on this device.  Enqueues on torch's current stream, no sync."""
+        import torch
+
+        if not (theta.is_cuda and theta.dtype == torch.float64 and theta.is_contiguous() and theta.dim() == 2
+                and theta.shape[1] == self.d and theta.device.index == self.device):
+            raise ValueError("theta must be a contiguous float64 CUDA tensor (W, d) on the handle's device")
+        W = theta.shape[0]
+        if out is None:
+            out = torch.empty(W, dtype=torch.float64, device=theta.device)
+        stream = torch.cuda.current_stream(theta.device).cuda_stream
+        self._check(self._lib.bi_log_posterior(self._h, C.c_void_p(theta.data_ptr()), W, float(n_div), _lib.MODE[mode],
+                                               C.c_void_p(out.data_ptr()),
+                                               C.c_void_p(info.data_ptr()) if info is not None else None,
+                                               C.c_void_p(stream)), "bi_log_posterior")
+        return out
+
+    def predict_pc_tensor(self, theta):
+        import torch
+
+        W = theta.shape[0]
+        m = torch.empty((W, self.n_pc_total), dtype=torch.float64, device=theta.device)
+        v = torch.empty_like(m)
+        stream = torch.cuda.current_stream(theta.device).cuda_stream
+        self._check(self._lib.bi_predict_pc(self._h, C.c_void_p(theta.data_ptr()), W, C.c_void_p(m.data_ptr()),
+                                            C.c_void_p(v.data_ptr()), C.c_void_p(stream)), "bi_predict_pc")
+        return m, v
+
+
+def from_analysis(emulation_config, emulation_results, *, min, max, experimental_results=None, sigma_exp=None,
+                  device: int = 0, max_batch: int = 0) -> DeviceEmulator:
+    """Pack what ``mcmc.run_mcmc`` loads (mcmc.py:48-67) and upload it."""
+    from . import image as _image
+
+    img = _image.pack(emulation_config, emulation_results, min=min, max=max, experimental_results=experimental_results,
+                      sigma_exp=sigma_exp)
+    return DeviceEmulator(img, device=device, max_batch=max_batch)

@@ -1,0 +1,149 @@
+/* bi_b200.h -- C ABI of the B200-native MCMC log-posterior path.
+ *
+ * One shared library (libbi_b200.so, built from bayesian_inference_b200/csrc/ by nvcc for sm_100a) exports the
+ * functions below.  They are what a foreign-function binding of the reference's hot path would bind; each one cites
+ * the reference interface it replaces (paths relative to the reference checkout, src/bayesian_inference/).
+ *
+ *   reference                                                     this ABI
+ *   ------------------------------------------------------------  -------------------------------------------
+ *   log_posterior.initialize_pool_variables  log_posterior.py:26   bi_create            (load once into HBM)
+ *   emulator.predict(X, return_std=True) xP  emulation.py:496-499  bi_predict_pc[_host]
+ *   sklearn kernel_(X, X_train_)             _gpr.py:446           bi_kernel_vectors[_host]
+ *   emulation.predict_emulation_group        emulation.py:466-548  bi_predict_group[_host]
+ *   emulation.predict (merged)               emulation.py:410-462  bi_predict[_host]
+ *   log_posterior.log_posterior              log_posterior.py:42   bi_log_posterior[_host]
+ *   log_posterior._loglikelihood             log_posterior.py:104  bi_loglikelihood_host
+ *
+ * Conventions
+ *   - every matrix is row-major float64; every index is 0-based;
+ *   - bi_desc / bi_group_desc carry HOST pointers; bi_create copies them to the device and builds the device image
+ *     (L^-1 per principal component, tiled Sigma_exp / unexplained covariance / inverse-PCA matrices);
+ *   - functions without the _host suffix take DEVICE pointers on the handle's device, enqueue on `stream`
+ *     (a cudaStream_t passed as void*, NULL = the handle's own stream) and return without synchronising;
+ *   - functions with the _host suffix take HOST pointers, copy in, run, copy out and synchronise before returning;
+ *   - return value: 0 = ok, < 0 = BI_E_* (bad argument / state), > 0 = a cudaError_t value.
+ *     bi_last_error(h) returns a static description of the last failure on that handle;
+ *   - a handle is not re-entrant: one host thread per handle (the reference: one process per pool worker).
+ *
+ * There is no CPU fallback behind this ABI.
+ */
+#ifndef BI_B200_H
+#define BI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BI_ABI_VERSION 1
+
+/* stationary kernel of one principal component's GP (sklearn kernels.py:1685-1712 Matern, :1530-1545 RBF) */
+#define BI_KERNEL_MATERN12 0 /* exp(-r)                               */
+#define BI_KERNEL_MATERN32 1 /* (1 + sqrt3 r) exp(-sqrt3 r)           */
+#define BI_KERNEL_MATERN52 2 /* (1 + sqrt5 r + 5 r^2 / 3) exp(-sqrt5 r) */
+#define BI_KERNEL_RBF      3 /* exp(-r^2 / 2)                         */
+
+/* how the per-walker covariance is factorised in bi_log_posterior */
+#define BI_MODE_DENSE      0 /* full F x F blocked Cholesky, no structure assumed (what the reference's dpotrf does)  */
+#define BI_MODE_STRUCTURED 1 /* skips tiles that are structurally zero (block-diagonal-per-observable covariance);   */
+                             /* falls back to nothing: refused with BI_E_STRUCTURE if Sigma_exp couples observables  */
+#define BI_MODE_WOODBURY   2 /* matrix-determinant-lemma / Woodbury: n_pc x n_pc factorisation per observable block   */
+
+#define BI_E_ARG        (-1) /* NULL / out-of-range argument            */
+#define BI_E_STATE      (-2) /* handle lacks what the call needs (e.g. no experimental data for log_posterior) */
+#define BI_E_STRUCTURE  (-3) /* structured / Woodbury mode requested but Sigma_exp couples observable blocks   */
+#define BI_E_UNSUPPORTED (-4)
+#define BI_E_NOMEM      (-5)
+
+/* One emulation group: the fitted objects of emulation.py:181-190, flattened. */
+typedef struct bi_group_desc {
+    int32_t n_design;        /* N   rows of X_train_                                           */
+    int32_t n_pc;            /* P   retained principal components = number of GPs              */
+    int32_t n_features;      /* F_g columns of pca.components_                                 */
+    int32_t n_rest;          /* Q-P truncated principal components (rows of S_rest)            */
+    const double*  X;        /* (N, d)    gpr.X_train_ (shared by all PCs, copy_X_train=False) */
+    const int32_t* kind;     /* (P)       BI_KERNEL_*                                          */
+    const double*  ell;      /* (P, d)    anisotropic length scales                            */
+    const double*  constant; /* (P)       ConstantKernel value, 0 if absent                    */
+    const double*  noise;    /* (P)       WhiteKernel level, 0 if absent                       */
+    const double*  alpha;    /* (P, N)    gpr.alpha_                                           */
+    const double*  L;        /* (P, N, N) gpr.L_, lower triangle used                          */
+    const double*  S;        /* (P, F_g)  pca.components_[:P]                                  */
+    const double*  S_rest;   /* (Q-P, F_g) pca.components_[P:]   (may be NULL when n_rest==0)  */
+    const double*  ev_rest;  /* (Q-P)     pca.explained_variance_[P:]                          */
+    const double*  scale;    /* (F_g)     scaler.scale_                                        */
+    const double*  mean;     /* (F_g)     scaler.mean_                                         */
+} bi_group_desc;
+
+/* Everything initialize_pool_variables (log_posterior.py:26-38) installs, flattened. */
+typedef struct bi_desc {
+    int32_t abi_version;     /* BI_ABI_VERSION                                                              */
+    int32_t device;          /* CUDA device ordinal                                                         */
+    int32_t d;               /* parameter dimension                                                         */
+    int32_t n_groups;
+    int32_t n_blocks;        /* B observable blocks                                                         */
+    int32_t n_features;      /* F width of the merged matrices                                              */
+    const bi_group_desc* groups;
+    const int64_t* blocks;   /* (B, 4) rows [group, out_start, in_start, len] (emulation.py:362-404)        */
+    const double*  prior_min;/* (d) strict bounds (log_posterior.py:63)                                     */
+    const double*  prior_max;/* (d)                                                                         */
+    const double*  y;        /* (F) experimental central values, NULL for predict-only handles              */
+    const double*  y_err;    /* (F) Sigma_exp = diag(y_err^2) (log_posterior.py:94) unless sigma_exp given  */
+    const double*  sigma_exp;/* (F, F) dense experimental covariance or NULL                                */
+    int32_t max_batch;       /* walkers processed per internal pass (0 = default 4096); bounds scratch HBM  */
+    int32_t reserved;
+} bi_desc;
+
+typedef struct bi_handle_s* bi_handle;
+
+int  bi_abi_version(void);
+int  bi_create(const bi_desc* desc, bi_handle* out);
+void bi_destroy(bi_handle h);
+const char* bi_last_error(bi_handle h);
+/* query: what = 0 F, 1 total n_pc, 2 d, 3 n_groups, 4 SM count, 5 Cholesky CTAs resident, 6 scratch bytes,
+ *        7 kernels launched since create (launch counter used by bench.py's gpu_launches)                  */
+int64_t bi_query(bi_handle h, int what);
+/* synchronise the handle's own stream */
+int  bi_sync(bi_handle h);
+
+/* k[w][p][j] = kernel_p(theta_w, X_j) of group g: out (W, P_g, N_g).  sklearn _gpr.py:446. */
+int bi_kernel_vectors(bi_handle h, int group, const double* theta, int64_t W, double* k_out, void* stream);
+int bi_kernel_vectors_host(bi_handle h, int group, const double* theta, int64_t W, double* k_out);
+
+/* GP mean and variance of every principal component of every group, concatenated in group order:
+ * m_out, v_out (W, P_total).  emulation.py:496-499 (v = std**2 after sklearn's clip at 0). */
+int bi_predict_pc(bi_handle h, const double* theta, int64_t W, double* m_out, double* v_out, void* stream);
+int bi_predict_pc_host(bi_handle h, const double* theta, int64_t W, double* m_out, double* v_out);
+
+/* One group in its own feature order: mean_out (W, F_g), cov_out (W, F_g, F_g) or NULL.
+ * n_div divides the unexplained covariance (emulation.py:493,531-532: rows in the call); pass 1 for MCMC. */
+int bi_predict_group(bi_handle h, int group, const double* theta, int64_t W, double n_div,
+                     double* mean_out, double* cov_out, void* stream);
+int bi_predict_group_host(bi_handle h, int group, const double* theta, int64_t W, double n_div,
+                          double* mean_out, double* cov_out);
+
+/* Merged prediction in sorted-observable order: mean_out (W, F); cov_out (W, F, F) block-diagonal per observable,
+ * or NULL.  emulation.py:410-462 + :346-406. */
+int bi_predict(bi_handle h, const double* theta, int64_t W, double n_div, double* mean_out, double* cov_out,
+               void* stream);
+int bi_predict_host(bi_handle h, const double* theta, int64_t W, double n_div, double* mean_out, double* cov_out);
+
+/* log-posterior of W walkers: logp_out (W) (-inf outside the strict prior box, NaN where the covariance is not
+ * positive definite), info_out (W) int32 or NULL (0 ok, k>0 = first non-positive pivot, 1-based, -1 outside prior).
+ * n_div <= 0 means "rows inside the prior box in this call" (what a batched reference call does,
+ * log_posterior.py:67,80 + emulation.py:493); MCMC passes 1. */
+int bi_log_posterior(bi_handle h, const double* theta, int64_t W, double n_div, int mode,
+                     double* logp_out, int32_t* info_out, void* stream);
+int bi_log_posterior_host(bi_handle h, const double* theta, int64_t W, double n_div, int mode,
+                          double* logp_out, int32_t* info_out);
+
+/* -1/2 dy^T C^-1 dy - sum log diag chol(C) for n explicit (dy, C) pairs: dy (n, F'), cov (n, F', F').
+ * log_posterior.py:104-146.  F' is arbitrary (need not equal the handle's F). */
+int bi_loglikelihood_host(bi_handle h, const double* dy, const double* cov, int64_t n, int32_t Fdim,
+                          double* out, int32_t* info_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BI_B200_H */
