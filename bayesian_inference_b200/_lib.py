@@ -20,7 +20,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
               "-Xcompiler", "-fPIC", "-shared"]
 
 EXPORTS = [
-    "bi_abi_version", "bi_create", "bi_destroy", "bi_last_error", "bi_query", "bi_sync",
+    "bi_abi_version", "bi_create", "bi_destroy", "bi_last_error", "bi_query", "bi_sync", "bi_profile", "bi_profile_read",
     "bi_kernel_vectors", "bi_kernel_vectors_host", "bi_predict_pc", "bi_predict_pc_host",
     "bi_predict_group", "bi_predict_group_host", "bi_predict", "bi_predict_host",
     "bi_log_posterior", "bi_log_posterior_host", "bi_loglikelihood_host",
@@ -111,6 +111,10 @@ def load() -> C.CDLL:
     lib.bi_query.restype = i64
     lib.bi_sync.argtypes = [h]
     lib.bi_sync.restype = C.c_int
+    lib.bi_profile.argtypes = [h, C.c_int]
+    lib.bi_profile.restype = C.c_int
+    lib.bi_profile_read.argtypes = [h, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    lib.bi_profile_read.restype = C.c_int
     lib.bi_kernel_vectors.argtypes = [h, C.c_int, dp, i64, dp, C.c_void_p]
     lib.bi_kernel_vectors_host.argtypes = [h, C.c_int, dp, i64, dp]
     lib.bi_predict_pc.argtypes = [h, dp, i64, dp, dp, C.c_void_p]
@@ -122,7 +126,7 @@ def load() -> C.CDLL:
     lib.bi_log_posterior.argtypes = [h, dp, i64, C.c_double, C.c_int, dp, dp, C.c_void_p]
     lib.bi_log_posterior_host.argtypes = [h, dp, i64, C.c_double, C.c_int, dp, dp]
     lib.bi_loglikelihood_host.argtypes = [h, dp, dp, i64, C.c_int32, dp, dp]
-    for name in EXPORTS[6:]:
+    for name in EXPORTS[8:]:
         getattr(lib, name).restype = C.c_int
     if lib.bi_abi_version() != 1:
         raise BackendUnavailable(f"ABI version mismatch: library {lib.bi_abi_version()}, package 1")

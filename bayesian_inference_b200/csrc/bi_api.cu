@@ -59,6 +59,10 @@ struct bi_handle_s {
     size_t out_scratch_bytes = 0;
     long long launches = 0;
     size_t scratch_bytes = 0;
+    bool profiling = false;
+    std::vector<std::array<cudaEvent_t, 2>> prof_events[2];   // [0] gp_predict, [1] chol_loglik
+    double prof_ms[2] = {0.0, 0.0};
+    long long prof_n[2] = {0, 0};
     std::string err;
 };
 
@@ -123,9 +127,24 @@ int build_a_tiles(bi_handle h, double n_div, cudaStream_t s) {
     return 0;
 }
 
+struct ProfScope {
+    bi_handle h; int k; cudaStream_t s; cudaEvent_t e1 = nullptr;
+    ProfScope(bi_handle h_, int k_, cudaStream_t s_) : h(h_), k(k_), s(s_) {
+        if (!h->profiling) return;
+        cudaEvent_t e0;
+        cudaEventCreate(&e0); cudaEventCreate(&e1);
+        cudaEventRecord(e0, s);
+        h->prof_events[k].push_back({e0, e1});
+    }
+    ~ProfScope() { if (e1) cudaEventRecord(e1, s); }
+};
+
 int launch_gp(bi_handle h, const double* dTheta, long long W, double* dM, double* dV, cudaStream_t s) {
     dim3 grid((unsigned)((W + GP_WT - 1) / GP_WT), (unsigned)h->Ptot);
-    gp_predict_kernel<true><<<grid, GP_THREADS, h->gp_smem, s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
+    {
+        ProfScope ps(h, 0, s);
+        gp_predict_kernel<true><<<grid, GP_THREADS, h->gp_smem, s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
+    }
     h->launches++;
     CK(cudaGetLastError());
     return 0;
@@ -141,8 +160,12 @@ int launch_chol(bi_handle h, const double* dTheta, const double* dM, const doubl
     P.kmin = (mode == BI_MODE_DENSE) ? h->dKminDense : h->dKminStruct;
     P.imax = (mode == BI_MODE_DENSE) ? h->dImaxDense : h->dImaxStruct;
     P.ws = h->dWs; P.ws_stride = h->ws_stride; P.logp = dLogp; P.info = dInfo; P.check_prior = 1;
+    P.cov_x = nullptr; P.dy_x = nullptr;
     const int grid = (int)std::min<long long>(W, h->chol_ctas);
-    chol_loglik_kernel<<<grid, CHOL_THREADS, h->chol_smem, s>>>(P);
+    {
+        ProfScope ps(h, 1, s);
+        chol_loglik_kernel<false><<<grid, CHOL_THREADS, h->chol_smem, s>>>(P);
+    }
     h->launches++;
     CK(cudaGetLastError());
     return 0;
@@ -169,6 +192,28 @@ int64_t bi_query(bi_handle h, int what) {
         case 7: return h->launches;
         default: return -1;
     }
+}
+
+int bi_profile(bi_handle h, int enable) {
+    if (!h) return BI_E_ARG;
+    h->profiling = enable != 0;
+    return 0;
+}
+
+int bi_profile_read(bi_handle h, int kernel, double* total_ms, int64_t* n_launches) {
+    if (!h || kernel < 0 || kernel > 1 || !total_ms || !n_launches) return BI_E_ARG;
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    for (auto& ev : h->prof_events[kernel]) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ev[0], ev[1]) == cudaSuccess) { h->prof_ms[kernel] += ms; h->prof_n[kernel]++; }
+        cudaEventDestroy(ev[0]); cudaEventDestroy(ev[1]);
+    }
+    h->prof_events[kernel].clear();
+    *total_ms = h->prof_ms[kernel];
+    *n_launches = h->prof_n[kernel];
+    h->prof_ms[kernel] = 0.0; h->prof_n[kernel] = 0;
+    return 0;
 }
 
 int bi_sync(bi_handle h) {
@@ -455,9 +500,9 @@ int bi_create(const bi_desc* D, bi_handle* out) {
     }
     if (h->has_data) {
         h->chol_smem = chol_smem_bytes(Fp, h->K0);
-        CKB(cudaFuncSetAttribute(chol_loglik_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chol_smem));
+        CKB(cudaFuncSetAttribute(chol_loglik_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chol_smem));
         int occ = 0;
-        CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_loglik_kernel, CHOL_THREADS, h->chol_smem));
+        CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_loglik_kernel<false>, CHOL_THREADS, h->chol_smem));
         if (occ < 1) {
             h->err = "Cholesky kernel does not fit on an SM";
             return bail(BI_E_UNSUPPORTED);
@@ -689,8 +734,51 @@ int bi_log_posterior_host(bi_handle h, const double* theta, int64_t W, double n_
     return 0;
 }
 
-int bi_loglikelihood_host(bi_handle h, const double*, const double*, int64_t, int32_t, double*, int32_t*) {
-    return fail(h, BI_E_UNSUPPORTED, "bi_loglikelihood_host: not implemented yet");
+int bi_loglikelihood_host(bi_handle h, const double* dy, const double* cov, int64_t n, int32_t Fdim, double* out,
+                          int32_t* info_out) {
+    if (!h || !dy || !cov || !out || n < 0 || Fdim <= 0) return fail(h, BI_E_ARG, "bad argument");
+    if (n == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    const int F = Fdim, nt = (F + 31) / 32, Fp = nt * 32;
+    const size_t smem = chol_smem_bytes(Fp, 4);
+    CK(cudaFuncSetAttribute(chol_loglik_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_loglik_kernel<true>, CHOL_THREADS, smem));
+    if (occ < 1) return fail(h, BI_E_UNSUPPORTED, "matrix too large for the Cholesky kernel's shared memory");
+    const long long per = (long long)F * F * 8;
+    const long long chunk = std::max<long long>(1, std::min<long long>(n, (512ll << 20) / per));
+    const int ctas = (int)std::min<long long>(chunk, (long long)h->sm_count * occ);
+    const long long stride = chol_ws_doubles(nt);
+    double *dCov = nullptr, *dDy = nullptr, *dWs = nullptr, *dLp = nullptr;
+    int *dInfo = nullptr, *dK = nullptr;
+    std::vector<int> kd((size_t)2 * nt, 0);
+    for (int i = 0; i < nt; ++i) kd[(size_t)nt + i] = nt - 1;
+    cudaError_t e = cudaSuccess;
+    auto A = [&](void** p, size_t b) { if (e == cudaSuccess) e = cudaMalloc(p, b); };
+    A((void**)&dCov, (size_t)chunk * per); A((void**)&dDy, (size_t)chunk * F * 8); A((void**)&dWs, (size_t)ctas * stride * 8);
+    A((void**)&dLp, (size_t)chunk * 8); A((void**)&dInfo, (size_t)chunk * 4); A((void**)&dK, kd.size() * 4);
+    int rc = 0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dK, kd.data(), kd.size() * 4, cudaMemcpyHostToDevice, h->stream);
+    for (long long w0 = 0; w0 < n && e == cudaSuccess; w0 += chunk) {
+        const long long wb = std::min<long long>(chunk, n - w0);
+        e = cudaMemcpyAsync(dCov, cov + (size_t)w0 * F * F, (size_t)wb * per, cudaMemcpyHostToDevice, h->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dDy, dy + (size_t)w0 * F, (size_t)wb * F * 8, cudaMemcpyHostToDevice, h->stream);
+        if (e != cudaSuccess) break;
+        CholParams P;
+        std::memset(&P, 0, sizeof(P));
+        P.F = F; P.Fp = Fp; P.nt = nt; P.K0 = 4; P.nks0 = 1; P.Ptot = 0; P.d = h->d; P.W = wb;
+        P.kmin = dK; P.imax = dK + nt; P.ws = dWs; P.ws_stride = stride; P.logp = dLp; P.info = dInfo;
+        P.cov_x = dCov; P.dy_x = dDy;
+        chol_loglik_kernel<true><<<(int)std::min<long long>(wb, ctas), CHOL_THREADS, smem, h->stream>>>(P);
+        h->launches++;
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaMemcpyAsync(out + w0, dLp, (size_t)wb * 8, cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess && info_out) e = cudaMemcpyAsync(info_out + w0, dInfo, (size_t)wb * 4, cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    }
+    if (e != cudaSuccess) { h->err = std::string("bi_loglikelihood_host: ") + cudaGetErrorString(e); rc = (int)e; }
+    cudaFree(dCov); cudaFree(dDy); cudaFree(dWs); cudaFree(dLp); cudaFree(dInfo); cudaFree(dK);
+    return rc;
 }
 
 }  // extern "C"

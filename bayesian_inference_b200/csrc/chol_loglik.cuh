@@ -46,6 +46,9 @@ struct CholParams {
     double* logp;             // (W)
     int* info;                // (W) or nullptr
     int check_prior;          // 1: strict prior box -> -inf ; 0: rows are known to be inside
+    // EXPLICIT instantiation only (log_posterior._loglikelihood(y, cov), log_posterior.py:104):
+    const double* cov_x;      // (W, F, F) row-major, lower triangle read
+    const double* dy_x;       // (W, F)
 };
 
 constexpr int CHOL_WARPS = 8;
@@ -118,6 +121,9 @@ __device__ __forceinline__ int warp_potrf_inv(double* sD, double* sLinv, double*
     return 0;
 }
 
+// EXPLICIT = false: covariance assembled on the fly from the emulator image (the log-posterior path).
+// EXPLICIT = true : covariance and residual given per row (the _loglikelihood(y, cov) entry point); no chunk 0.
+template <bool EXPLICIT>
 __global__ void __launch_bounds__(CHOL_THREADS, 2) chol_loglik_kernel(const CholParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* sNegV = reinterpret_cast<double*>(smem_raw);
@@ -142,13 +148,14 @@ __global__ void __launch_bounds__(CHOL_THREADS, 2) chol_loglik_kernel(const Chol
     double* wsL = P.ws + (long long)blockIdx.x * P.ws_stride;
     double* wsZ = wsL + (long long)nt * (nt - 1) / 2 * TILE_ELEMS;
 
-    for (int r = tid; r < P.Fp; r += CHOL_THREADS) sObs[r] = P.obs_id[r];
+    if (!EXPLICIT)
+        for (int r = tid; r < P.Fp; r += CHOL_THREADS) sObs[r] = P.obs_id[r];
 
     for (long long w = blockIdx.x; w < P.W; w += gridDim.x) {
         __syncthreads();   // previous walker fully done with smem
         if (tid == 0) {
             int inside = 1;
-            if (P.check_prior) {
+            if (!EXPLICIT && P.check_prior) {
                 for (int k = 0; k < P.d; ++k) {
                     const double x = P.theta[w * P.d + k];
                     if (!(x > P.prior_min[k] && x < P.prior_max[k])) inside = 0;
@@ -157,11 +164,12 @@ __global__ void __launch_bounds__(CHOL_THREADS, 2) chol_loglik_kernel(const Chol
             sFlag[0] = inside;
             sFlag[1] = 0;   // failure index
         }
-        for (int q = tid; q < P.K0; q += CHOL_THREADS) {
-            const bool ok = q < P.Ptot;
-            sM[q] = ok ? P.m[w * P.Ptot + q] : 0.0;
-            sNegV[q] = ok ? -P.v[w * P.Ptot + q] : 0.0;
-        }
+        if (!EXPLICIT)
+            for (int q = tid; q < P.K0; q += CHOL_THREADS) {
+                const bool ok = q < P.Ptot;
+                sM[q] = ok ? P.m[w * P.Ptot + q] : 0.0;
+                sNegV[q] = ok ? -P.v[w * P.Ptot + q] : 0.0;
+            }
         __syncthreads();
         if (!sFlag[0]) {
             if (tid == 0) {
@@ -172,8 +180,13 @@ __global__ void __launch_bounds__(CHOL_THREADS, 2) chol_loglik_kernel(const Chol
         }
         // dY = T m + (mu - y)      (emulation.py:506-509 + log_posterior.py:87)
         for (int r = tid; r < P.Fp; r += CHOL_THREADS) {
-            double s = __ldg(P.e + r);
-            for (int q = 0; q < P.K0; ++q) s = fma(__ldg(P.Tt + (long long)q * P.Fp + r), sM[q], s);
+            double s;
+            if (EXPLICIT) {
+                s = (r < P.F) ? P.dy_x[w * P.F + r] : 0.0;
+            } else {
+                s = __ldg(P.e + r);
+                for (int q = 0; q < P.K0; ++q) s = fma(__ldg(P.Tt + (long long)q * P.Fp + r), sM[q], s);
+            }
             sDy[r] = s;
         }
         __syncthreads();
@@ -186,7 +199,7 @@ __global__ void __launch_bounds__(CHOL_THREADS, 2) chol_loglik_kernel(const Chol
             const int i_hi = P.imax[j];
             const int nreg = 2 * (i_hi - j + 1);   // regular 16-row units of this panel
             const int nunits = nreg + 1;           // + the dY row
-            const int omin_j = P.tile_omin[j];
+            const int omin_j = EXPLICIT ? 0 : P.tile_omin[j];
 
             // ---------------- phase 1: update every unit of the panel -----------------------------------------
             for (int q = warp; q < nunits; q += CHOL_WARPS) {
@@ -200,7 +213,7 @@ __global__ void __launch_bounds__(CHOL_THREADS, 2) chol_loglik_kernel(const Chol
                     for (int nf = 0; nf < 4; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
 
                 const int k_lo = P.kmin[is_z ? j : i];   // the dY row is dense; L_jk is not
-                if (!is_z) {
+                if (!EXPLICIT && !is_z) {
                     if (P.tile_omax[j] >= P.tile_omin[i]) {
                         // chunk 0: -T_i D T_j^T, masked to pairs of rows of the same observable (emulation.py:362-388)
                         const double* At = P.Tm + (long long)i * tstride + (long long)(2 * h) * nks0 * 32 + lane;
@@ -266,6 +279,20 @@ __global__ void __launch_bounds__(CHOL_THREADS, 2) chol_loglik_kernel(const Chol
                                 const double init = (mi == 0 && g == 0) ? sDy[j * 32 + nf * 8 + 2 * t + e] : 0.0;
                                 acc[mi][nf][e] = init - acc[mi][nf][e];
                             }
+                } else if (EXPLICIT) {
+                    const double* Cw = P.cov_x + w * (long long)P.F * P.F;
+#pragma unroll
+                    for (int mi = 0; mi < 2; ++mi) {
+                        const int r = i * 32 + (2 * h + mi) * 8 + g;
+#pragma unroll
+                        for (int nf = 0; nf < 4; ++nf)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const int c = j * 32 + nf * 8 + 2 * t + e;
+                                const double init = (r < P.F && c < P.F) ? Cw[(long long)r * P.F + c] : (r == c ? 1.0 : 0.0);
+                                acc[mi][nf][e] = init - acc[mi][nf][e];
+                            }
+                    }
                 } else {
                     const double2* At = reinterpret_cast<const double2*>(
                         P.Atiles + ((long long)i * (i + 1) / 2 + j) * TILE_ELEMS);

@@ -109,6 +109,15 @@ class DeviceEmulator:
         """Kernels launched by this handle since creation."""
         return self.query(7)
 
+    def profile(self, enable: bool = True) -> None:
+        self._check(self._lib.bi_profile(self._h, int(enable)), "bi_profile")
+
+    def profile_read(self, kernel: int) -> tuple[float, int]:
+        """(summed device ms, launches) of kernel 0 = gp_predict, 1 = chol_loglik since the last read."""
+        ms, n = C.c_double(), C.c_int64()
+        self._check(self._lib.bi_profile_read(self._h, kernel, C.byref(ms), C.byref(n)), "bi_profile_read")
+        return ms.value, n.value
+
     def sync(self) -> None:
         self._check(self._lib.bi_sync(self._h), "bi_sync")
 

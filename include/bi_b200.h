@@ -106,6 +106,11 @@ const char* bi_last_error(bi_handle h);
 int64_t bi_query(bi_handle h, int what);
 /* synchronise the handle's own stream */
 int  bi_sync(bi_handle h);
+/* per-kernel device timing with CUDA events recorded on the launching stream (used by bench.py's roofline):
+ * bi_profile(h, 1) starts recording; bi_profile_read synchronises the device, returns and resets the summed duration
+ * and launch count of kernel 0 = gp_predict (K1+K2) or 1 = chol_loglik (K4). */
+int  bi_profile(bi_handle h, int enable);
+int  bi_profile_read(bi_handle h, int kernel, double* total_ms, int64_t* n_launches);
 
 /* k[w][p][j] = kernel_p(theta_w, X_j) of group g: out (W, P_g, N_g).  sklearn _gpr.py:446. */
 int bi_kernel_vectors(bi_handle h, int group, const double* theta, int64_t W, double* k_out, void* stream);

@@ -1,0 +1,60 @@
+"""The reference-facing Python modules (emulation.predict, log_posterior.log_posterior) on real sklearn objects."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+from conftest import fro_err, load_golden, rel_err
+
+from bayesian_inference_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def toy():
+    return synthetic.generate("TOY", oob_fraction=0.1)
+
+
+def test_emulation_predict_signature_and_values(toy):
+    from bayesian_inference_b200 import emulation
+
+    _, ref = load_golden("toy")
+    th = toy.theta[:24]
+    out = emulation.predict(th, toy.emulation_config, emulation_group_results=toy.emulation_results)
+    assert set(out) == {"central_value", "cov"}
+    assert fro_err(out["central_value"], ref["ref_mean"]) < 1e-12 and fro_err(out["cov"], ref["ref_cov"]) < 1e-12
+    per = emulation.predict(th, toy.emulation_config, merge_predictions_over_groups=False,
+                            emulation_group_results=toy.emulation_results)
+    assert list(per) == ["alpha", "beta"]
+    for gi, g in enumerate(per):
+        assert fro_err(per[g]["cov"], ref[f"ref_g{gi}_cov"]) < 1e-12
+    gcfg = toy.emulation_config.emulation_groups_config["alpha"]
+    one = emulation.predict_emulation_group(th, toy.emulation_results["alpha"], gcfg)
+    assert fro_err(one["central_value"], ref["ref_g0_mean"]) < 1e-12 and fro_err(one["cov"], ref["ref_g0_cov"]) < 1e-12
+    emulation.clear_cache()
+
+
+def test_log_posterior_module_is_a_drop_in(toy):
+    from bayesian_inference_b200 import log_posterior as lp
+
+    _, ref = load_golden("toy")
+    lp.initialize_pool_variables(toy.min, toy.max, toy.emulation_config, toy.emulation_results,
+                                 toy.experimental_results, None)
+    th = toy.theta[:24]
+    batch = lp.log_posterior(th)
+    fin = np.isfinite(ref["ref_logp_batch"])
+    assert np.array_equal(np.isneginf(batch), ~fin) and rel_err(batch[fin], ref["ref_logp_batch"][fin]) < 1e-9
+    rows = np.array([lp.log_posterior(x)[0] for x in th])        # emcee without vectorize: (d,) in, (1,) out
+    assert rel_err(rows[fin], ref["ref_logp_rows"][fin]) < 1e-9
+    assert np.array_equal(lp.log_posterior_walkers(th), rows)
+    assert lp.log_posterior(list(th[0])).shape == (1,)           # list input (numpy>=2 breaks the reference here, F13)
+    # _loglikelihood(y, cov) on the merged prediction reproduces the same number
+    from bayesian_inference_b200 import emulation
+
+    i = int(np.flatnonzero(fin)[0])
+    pred = emulation.predict(th[i:i + 1], toy.emulation_config, emulation_group_results=toy.emulation_results)
+    y, ye = toy.experimental_results["y"], toy.experimental_results["y_err"]
+    val = lp._loglikelihood(pred["central_value"][0] - y, pred["cov"][0] + np.diag(ye ** 2))
+    assert abs(val - ref["ref_logp_rows"][i]) < 1e-9 * abs(ref["ref_logp_rows"][i])
+    lp.close()
+    emulation.clear_cache()

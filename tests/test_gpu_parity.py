@@ -1,0 +1,202 @@
+"""Parity of the CUDA path (through the C ABI) with the reference's golden vectors and with the numpy oracle.
+
+Tolerances (SURVEY §8c / BASELINE north_star): kernel vector <= 1e-13 rel, PC mean <= 1e-11 (scaled), PC variance
+<= 1e-11 * kernel diag abs, observable mean / covariance <= 1e-12 rel (Frobenius), log-posterior <= 1e-9 rel."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+from conftest import fro_err, load_golden, rel_err
+
+from bayesian_inference_b200 import image, synthetic
+from oracle import closed_form as cf
+
+pytestmark = pytest.mark.gpu
+
+TOL_K, TOL_PC, TOL_OBS, TOL_LOGP = 1e-13, 1e-11, 1e-12, 1e-9
+
+
+def _dev(z):
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    return DeviceEmulator(image.EmulatorImage.from_flat(z))
+
+
+def _cmp_logp(got, want, tol=TOL_LOGP):
+    assert np.array_equal(np.isneginf(got), np.isneginf(want))
+    fin = np.isfinite(want)
+    assert np.all(np.isfinite(got[fin]))
+    assert rel_err(got[fin], want[fin]) < tol
+
+
+# ---- golden fixtures (outputs of the reference itself) ------------------------------------------------------------
+def test_golden_kernel_vectors(golden):
+    _, z, ref = golden
+    with _dev(z) as dev:
+        for g in range(int(z["n_groups"])):
+            assert rel_err(dev.kernel_vectors(g, ref["theta"]), ref[f"ref_kvec_g{g}"]) < TOL_K
+
+
+def test_golden_pc_mean_variance(golden):
+    _, z, ref = golden
+    with _dev(z) as dev:
+        m, v = dev.predict_pc(ref["theta"])
+    assert np.max(np.abs(m - ref["ref_pc_mean"])) < TOL_PC * max(1.0, np.max(np.abs(ref["ref_pc_mean"])))
+    diag = np.concatenate([1.0 + z[f"g{g}_const"] + z[f"g{g}_noise"] for g in range(int(z["n_groups"]))])
+    assert np.max(np.abs(v - ref["ref_pc_var"]) / diag) < TOL_PC
+    assert np.all(v >= 0.0)
+
+
+def test_golden_predict(golden):
+    _, z, ref = golden
+    with _dev(z) as dev:
+        mean, cov = dev.predict(ref["theta"])                       # divisor = rows in the call, like the reference
+        assert fro_err(mean, ref["ref_mean"]) < TOL_OBS
+        assert fro_err(cov, ref["ref_cov"]) < TOL_OBS
+        assert np.array_equal(cov == 0.0, ref["ref_cov"] == 0.0)    # identical block-diagonal sparsity (F2)
+        for g in range(int(z["n_groups"])):
+            mg, cg = dev.predict_group(g, ref["theta"])
+            assert fro_err(mg, ref[f"ref_g{g}_mean"]) < TOL_OBS
+            assert fro_err(cg, ref[f"ref_g{g}_cov"]) < TOL_OBS
+
+
+def test_golden_log_posterior(golden):
+    name, z, ref = golden
+    with _dev(z) as dev:
+        _cmp_logp(dev.log_posterior(ref["theta"], n_div=None), ref["ref_logp_batch"])
+        _cmp_logp(dev.log_posterior(ref["theta"], n_div=1.0), ref["ref_logp_rows"])
+        rows = np.array([dev.log_posterior(t, n_div=None)[0] for t in ref["theta"]])      # how emcee drives it
+        _cmp_logp(rows, ref["ref_logp_rows"])
+        if name != "toy_dense_sigma":
+            _cmp_logp(dev.log_posterior(ref["theta"], n_div=1.0, mode="structured"), ref["ref_logp_rows"])
+
+
+def test_structured_mode_refused_when_sigma_couples_observables():
+    from bayesian_inference_b200.device import DeviceError
+
+    z, ref = load_golden("toy_dense_sigma")
+    F = int(z["n_features"])
+    z = dict(z)
+    z["sigma_exp"] = z["sigma_exp"] + 1e-3 * np.min(np.diag(z["sigma_exp"])) * np.ones((F, F))
+    with _dev(z) as dev:
+        with pytest.raises(DeviceError):
+            dev.log_posterior(ref["theta"], mode="structured")
+        want = cf.log_posterior(z, ref["theta"], n_div=1.0)
+        _cmp_logp(dev.log_posterior(ref["theta"], mode="dense"), want)
+
+
+# ---- generated analyses at the BASELINE shapes vs the oracle ------------------------------------------------------
+@pytest.mark.parametrize("name,n_check,over", [
+    ("C1", 16, {}),
+    ("C3A", 8, {}),
+    ("C3B", 6, {}),
+    ("C3A", 6, {"dense_sigma_exp": True}),
+    ("C4", 8, {"oob_fraction": 0.2}),
+])
+def test_generated_config_vs_oracle(name, n_check, over):
+    a = synthetic.generate(name, **over)
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max,
+                     experimental_results=a.experimental_results, sigma_exp=a.sigma_exp)
+    z = img.to_flat()
+    th = a.theta[:n_check]
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    with DeviceEmulator(img) as dev:
+        m, v = dev.predict_pc(th)
+        mo, vo = [np.concatenate(x, axis=1) for x in zip(*[cf.predict_pc(z, g, th) for g in range(len(img.groups))])]
+        assert np.max(np.abs(m - mo)) < TOL_PC * max(1.0, np.max(np.abs(mo)))
+        assert np.max(np.abs(v - vo)) < TOL_PC * 4.0
+        mean, cov = dev.predict(th[:4], n_div=1.0)
+        mo_, co_ = cf.predict(z, th[:4], n_div=1.0)
+        assert fro_err(mean, mo_) < TOL_OBS and fro_err(cov, co_) < TOL_OBS
+        want = cf.log_posterior(z, th, n_div=1.0)
+        _cmp_logp(dev.log_posterior(th, n_div=1.0), want)
+        if a.sigma_exp is None:
+            _cmp_logp(dev.log_posterior(th, n_div=1.0, mode="structured"), want)
+
+
+# ---- size-independent properties at the full BASELINE size ----------------------------------------------------------
+@pytest.fixture(scope="module")
+def c3a():
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    a = synthetic.generate("C3A", oob_fraction=0.01)
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max,
+                     experimental_results=a.experimental_results)
+    dev = DeviceEmulator(img)
+    yield a, img, dev
+    dev.close()
+
+
+def test_full_size_batch_equals_rows_and_is_deterministic(c3a):
+    a, _, dev = c3a
+    full = dev.log_posterior(a.theta, n_div=1.0)                         # 1024 walkers, one call
+    again = dev.log_posterior(a.theta, n_div=1.0)
+    assert np.array_equal(full, again, equal_nan=True)                   # bit-reproducible
+    idx = np.arange(0, a.theta.shape[0], 97)
+    rows = np.array([dev.log_posterior(a.theta[i], n_div=1.0)[0] for i in idx])
+    assert np.array_equal(rows, full[idx])                               # a walker's value does not depend on its batch
+    perm = np.random.default_rng(0).permutation(a.theta.shape[0])
+    assert np.array_equal(dev.log_posterior(a.theta[perm], n_div=1.0), full[perm])
+    assert np.count_nonzero(np.isneginf(full)) == np.count_nonzero(~np.all((a.theta > a.min) & (a.theta < a.max), axis=1))
+
+
+def test_full_size_dense_equals_structured(c3a):
+    a, _, dev = c3a
+    d = dev.log_posterior(a.theta, n_div=1.0, mode="dense")
+    s = dev.log_posterior(a.theta, n_div=1.0, mode="structured")
+    fin = np.isfinite(d)
+    assert np.array_equal(np.isneginf(d), np.isneginf(s)) and rel_err(s[fin], d[fin]) < TOL_LOGP
+
+
+def test_full_size_torch_device_path_matches_host_path(c3a):
+    import torch
+
+    a, _, dev = c3a
+    th = torch.from_numpy(a.theta).cuda()
+    out = dev.log_posterior_tensor(th, n_div=1.0)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), dev.log_posterior(a.theta, n_div=1.0))
+
+
+# ---- edge cases ---------------------------------------------------------------------------------------------------
+def test_edge_cases_empty_single_all_outside():
+    z, ref = load_golden("toy")
+    with _dev(z) as dev:
+        assert dev.log_posterior(np.empty((0, int(z["d"])))).shape == (0,)
+        one = dev.log_posterior(ref["theta"][0])
+        assert one.shape == (1,) and np.isfinite(one[0])
+        out = dev.log_posterior(np.full((5, int(z["d"])), 2.0), n_div=None)
+        assert np.all(np.isneginf(out))
+        th = np.tile(0.5 * (z["min"] + z["max"]), (3, 1))
+        th[1, 0] = z["max"][0]            # exactly on the boundary -> outside
+        th[2, 0] = np.nan                 # NaN compares false -> outside, as in the reference
+        lp, info = dev.log_posterior(th, return_info=True)
+        assert np.isfinite(lp[0]) and np.isneginf(lp[1]) and np.isneginf(lp[2])
+        assert list(info) == [0, -1, -1]
+        m, c = dev.predict(np.empty((0, int(z["d"]))))
+        assert m.shape == (0, int(z["n_features"])) and c.shape[0] == 0
+
+
+@pytest.mark.parametrize("F", [1, 5, 31, 32, 33, 64, 100, 257])
+def test_explicit_loglikelihood_matches_lapack(F):
+    z, _ = load_golden("toy")
+    rng = np.random.default_rng(F)
+    n = 5
+    A = rng.normal(size=(n, F, F))
+    cov = A @ np.swapaxes(A, 1, 2) + F * np.eye(F)
+    dy = rng.normal(size=(n, F))
+    with _dev(z) as dev:
+        got, info = dev.loglikelihood(dy, cov, return_info=True)
+    want = np.array([cf.log_likelihood(dy[i], cov[i]) for i in range(n)])
+    assert np.all(info == 0) and rel_err(got, want) < 1e-11
+
+
+def test_not_positive_definite_reports_pivot_and_nan():
+    z, _ = load_golden("toy")
+    F = 40
+    cov = np.eye(F)[None].repeat(2, 0)
+    cov[1, 36, 36] = -1.0
+    with _dev(z) as dev:
+        got, info = dev.loglikelihood(np.ones((2, F)), cov, return_info=True)
+    assert np.isfinite(got[0]) and np.isnan(got[1]) and info[0] == 0 and info[1] == 37
