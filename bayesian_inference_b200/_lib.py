@@ -13,7 +13,7 @@ from pathlib import Path
 
 PKG_DIR = Path(__file__).resolve().parent
 CSRC = PKG_DIR / "csrc"
-LIB_PATH = PKG_DIR / "libbi_b200.so"
+LIB_PATH = Path(os.environ.get("BI_B200_LIB") or PKG_DIR / "libbi_b200.so")   # override: developer A/B builds only
 HEADER = PKG_DIR.parent / "include" / "bi_b200.h"
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

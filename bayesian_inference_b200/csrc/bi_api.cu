@@ -5,12 +5,14 @@
 #include <array>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
 
 #include "../../include/bi_b200.h"
 #include "chol_loglik.cuh"
+#include "chol_pipe.cuh"
 #include "common.cuh"
 #include "cov_assemble.cuh"
 #include "gp_predict.cuh"
@@ -43,7 +45,9 @@ struct bi_handle_s {
     std::vector<double> hMin, hMax;
     bool has_data = false, sigma_blockdiag = true;
     double *dTrow = nullptr, *dTt = nullptr, *dTm = nullptr, *dE = nullptr, *dMeanMerged = nullptr, *dUblk = nullptr;
-    double *dSig = nullptr, *dYerr = nullptr, *dATiles = nullptr;
+    double *dSig = nullptr, *dYerr = nullptr, *dATiles = nullptr, *dTmP = nullptr;
+    int nTc = 0, chol_impl = 2;
+    size_t pipe_smem = 0;
     double a_ndiv = -1.0;
     int *dObs = nullptr, *dTileOmin = nullptr, *dTileOmax = nullptr;
     int *dKminDense = nullptr, *dImaxDense = nullptr, *dKminStruct = nullptr, *dImaxStruct = nullptr;
@@ -164,7 +168,13 @@ int launch_chol(bi_handle h, const double* dTheta, const double* dM, const doubl
     const int grid = (int)std::min<long long>(W, h->chol_ctas);
     {
         ProfScope ps(h, 1, s);
-        chol_loglik_kernel<false><<<grid, CHOL_THREADS, h->chol_smem, s>>>(P);
+        if (h->chol_impl == 2) {
+            PipeParams PP;
+            PP.c = P; PP.TmP = h->dTmP; PP.nTc = h->nTc;
+            chol_pipe_kernel<false><<<grid, PIPE_THREADS, h->pipe_smem, s>>>(PP);
+        } else {
+            chol_loglik_kernel<false><<<grid, CHOL_THREADS, h->chol_smem, s>>>(P);
+        }
     }
     h->launches++;
     CK(cudaGetLastError());
@@ -435,6 +445,14 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         TRY(upload(h, &h->dTrow, trow.data(), trow.size()));
         TRY(upload(h, &h->dTt, tt.data(), tt.size()));
         TRY(upload(h, &h->dTm, tm.data(), tm.size()));
+        h->nTc = (K0 + 31) / 32;
+        {
+            std::vector<double> tmp((size_t)nt * h->nTc * TILE_ELEMS, 0.0);
+            for (int r = 0; r < F; ++r)
+                for (int q = 0; q < h->Ptot; ++q)
+                    tmp[((size_t)(r / 32) * h->nTc + q / 32) * TILE_ELEMS + of_index(r % 32, q % 32, 8)] = trow[(size_t)r * K0 + q];
+            TRY(upload(h, &h->dTmP, tmp.data(), tmp.size()));
+        }
         TRY(upload(h, &h->dMeanMerged, mean.data(), mean.size()));
         TRY(upload(h, &h->dE, ev.data(), ev.size()));
         CKB(cudaStreamSynchronize(h->stream));
@@ -507,6 +525,17 @@ int bi_create(const bi_desc* D, bi_handle* out) {
             h->err = "Cholesky kernel does not fit on an SM";
             return bail(BI_E_UNSUPPORTED);
         }
+        if (const char* e = std::getenv("BI_CHOL_IMPL")) h->chol_impl = std::atoi(e) == 1 ? 1 : 2;
+        h->pipe_smem = pipe_smem_bytes(Fp, h->nTc * 32);
+        if (h->chol_impl == 2 && (h->pipe_smem > 227 * 1024 || nt > 120)) h->chol_impl = 1;
+        if (h->chol_impl == 2) {
+            CKB(cudaFuncSetAttribute(chol_pipe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pipe_smem));
+            CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_pipe_kernel<false>, PIPE_THREADS, h->pipe_smem));
+            if (occ < 1) {
+                h->err = "pipelined Cholesky kernel does not fit on an SM";
+                return bail(BI_E_UNSUPPORTED);
+            }
+        }
         h->chol_ctas = h->sm_count * occ;
         h->ws_stride = chol_ws_doubles(nt);
         TRY(dalloc(h, &h->dWs, (size_t)h->chol_ctas * h->ws_stride));
@@ -523,7 +552,7 @@ int bi_kernel_vectors(bi_handle h, int group, const double* theta, int64_t W, do
     if (!h || !theta || !k_out || W < 0 || group < 0 || group >= h->G) return fail(h, BI_E_ARG, "bad argument");
     if (W == 0) return 0;
     CK(cudaSetDevice(h->device));
-    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    cudaStream_t s = (cudaStream_t)stream;
     const GroupImg& I = h->groups[group];
     dim3 grid((unsigned)((W + GP_WT - 1) / GP_WT), (unsigned)I.P);
     gp_predict_kernel<false><<<grid, GP_THREADS, h->gp_smem, s>>>(h->dPcs, I.pc_off, h->d, theta, W, k_out, I.P, nullptr,
@@ -556,7 +585,7 @@ int bi_predict_pc(bi_handle h, const double* theta, int64_t W, double* m_out, do
     if (!h || !theta || !m_out || !v_out || W < 0) return fail(h, BI_E_ARG, "bad argument");
     if (W == 0) return 0;
     CK(cudaSetDevice(h->device));
-    return launch_gp(h, theta, W, m_out, v_out, stream ? (cudaStream_t)stream : h->stream);
+    return launch_gp(h, theta, W, m_out, v_out, (cudaStream_t)stream);
 }
 
 int bi_predict_pc_host(bi_handle h, const double* theta, int64_t W, double* m_out, double* v_out) {
@@ -609,7 +638,7 @@ static int predict_dev(bi_handle h, int group, const double* theta, int64_t W, d
     if (!h || !theta || W < 0 || group >= h->G || !(n_div > 0.0)) return fail(h, BI_E_ARG, "bad argument");
     if (W == 0) return 0;
     CK(cudaSetDevice(h->device));
-    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    cudaStream_t s = (cudaStream_t)stream;
     const int Fo = group < 0 ? h->F : h->groups[group].Fg;
     for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
         const long long wb = std::min<long long>(h->max_batch, W - w0);
@@ -677,7 +706,7 @@ int bi_log_posterior(bi_handle h, const double* theta, int64_t W, double n_div, 
     if (rc) return rc;
     if (W == 0) return 0;
     CK(cudaSetDevice(h->device));
-    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    cudaStream_t s = (cudaStream_t)stream;
     if (!(n_div > 0.0)) {
         // rows inside the prior box in this call (log_posterior.py:67 -> emulation.py:493); needs one readback
         CK(cudaMemsetAsync(h->dCount, 0, sizeof(unsigned long long), s));

@@ -51,6 +51,9 @@ struct CholParams {
     const double* dy_x;       // (W, F)
 };
 
+#ifndef CHOL_MIN_BLOCKS
+#define CHOL_MIN_BLOCKS 2
+#endif
 constexpr int CHOL_WARPS = 8;
 constexpr int CHOL_THREADS = CHOL_WARPS * 32;
 constexpr int TILE_ELEMS = BI_TILE * BI_TILE;  // 1024 doubles = 8 KB
@@ -124,7 +127,7 @@ __device__ __forceinline__ int warp_potrf_inv(double* sD, double* sLinv, double*
 // EXPLICIT = false: covariance assembled on the fly from the emulator image (the log-posterior path).
 // EXPLICIT = true : covariance and residual given per row (the _loglikelihood(y, cov) entry point); no chunk 0.
 template <bool EXPLICIT>
-__global__ void __launch_bounds__(CHOL_THREADS, 2) chol_loglik_kernel(const CholParams P) {
+__global__ void __launch_bounds__(CHOL_THREADS, CHOL_MIN_BLOCKS) chol_loglik_kernel(const CholParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* sNegV = reinterpret_cast<double*>(smem_raw);
     double* sM = sNegV + P.K0;

@@ -19,7 +19,8 @@
  *   - bi_desc / bi_group_desc carry HOST pointers; bi_create copies them to the device and builds the device image
  *     (L^-1 per principal component, tiled Sigma_exp / unexplained covariance / inverse-PCA matrices);
  *   - functions without the _host suffix take DEVICE pointers on the handle's device, enqueue on `stream`
- *     (a cudaStream_t passed as void*, NULL = the handle's own stream) and return without synchronising;
+ *     (a cudaStream_t passed as void*; NULL is CUDA's default stream, as everywhere in the runtime API) and return
+ *     without synchronising; their scratch buffers are per handle, so calls on one handle must be stream-ordered;
  *   - functions with the _host suffix take HOST pointers, copy in, run, copy out and synchronise before returning;
  *   - return value: 0 = ok, < 0 = BI_E_* (bad argument / state), > 0 = a cudaError_t value.
  *     bi_last_error(h) returns a static description of the last failure on that handle;
