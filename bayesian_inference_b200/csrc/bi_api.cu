@@ -170,8 +170,32 @@ int launch_chol(bi_handle h, const double* dTheta, const double* dM, const doubl
         ProfScope ps(h, 1, s);
         if (h->chol_impl == 2) {
             PipeParams PP;
-            PP.c = P; PP.TmP = h->dTmP; PP.nTc = h->nTc;
+            PP.c = P; PP.TmP = h->dTmP; PP.nTc = h->nTc; PP.dbg = nullptr;
+#ifdef PIPE_TIMING
+            static long long* dbg = nullptr;
+            if (!dbg) cudaMalloc(&dbg, 64 * 8);
+            cudaMemsetAsync(dbg, 0, 64 * 8, s);
+            PP.dbg = dbg;
+#endif
             chol_pipe_kernel<false><<<grid, PIPE_THREADS, h->pipe_smem, s>>>(PP);
+#ifdef PIPE_TIMING
+            {
+                long long hb[64];
+                cudaMemcpyAsync(hb, dbg, sizeof(hb), cudaMemcpyDeviceToHost, s);
+                cudaStreamSynchronize(s);
+                const char* nm[6] = {"wait_full", "sweep_mma", "epi_park/diag", "epi_fast_trsm", "wait_linv", "deferred+fence"};
+                double tot = 0;
+                for (int c = 0; c < 6; ++c) for (int wq = 0; wq < 8; ++wq) tot += (double)hb[wq * 8 + c];
+                std::fprintf(stderr, "[pipe timing] W=%lld grid=%d: ", (long long)W, grid);
+                for (int c = 0; c < 6; ++c) {
+                    double v = 0;
+                    for (int wq = 0; wq < 8; ++wq) v += (double)hb[wq * 8 + c];
+                    std::fprintf(stderr, "%s %.1f%%  ", nm[c], 100.0 * v / tot);
+                }
+                std::fprintf(stderr, " | cycles/walker/warp %.0f | factor warp: potrf %.0f cyc/panel, idle %.0f cyc/panel\n", tot / 8.0 / (double)W,
+                             (double)hb[6] / (double)W / h->nt, (double)hb[7] / (double)W / h->nt);
+            }
+#endif
         } else {
             chol_loglik_kernel<false><<<grid, CHOL_THREADS, h->chol_smem, s>>>(P);
         }
@@ -450,7 +474,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
             std::vector<double> tmp((size_t)nt * h->nTc * TILE_ELEMS, 0.0);
             for (int r = 0; r < F; ++r)
                 for (int q = 0; q < h->Ptot; ++q)
-                    tmp[((size_t)(r / 32) * h->nTc + q / 32) * TILE_ELEMS + of_index(r % 32, q % 32, 8)] = trow[(size_t)r * K0 + q];
+                    tmp[((size_t)(r / 32) * h->nTc + q / 32) * TILE_ELEMS + of2_index(r % 32, q % 32)] = trow[(size_t)r * K0 + q];
             TRY(upload(h, &h->dTmP, tmp.data(), tmp.size()));
         }
         TRY(upload(h, &h->dMeanMerged, mean.data(), mean.size()));

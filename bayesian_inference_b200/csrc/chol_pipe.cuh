@@ -1,17 +1,22 @@
 // chol_pipe.cuh -- K4 (v2): fused covariance assembly + blocked Cholesky + solve + log-det, warp-specialised and fed by
-// TMA bulk copies through an mbarrier ring.  Same mathematics and tile formats as chol_loglik.cuh (see there); what
-// changes is how operands reach the FP64 tensor pipe:
+// TMA bulk copies through an mbarrier ring.  Same mathematics as chol_loglik.cuh (see there); what changes is how
+// operands reach the FP64 tensor pipe:
 //
 //   warps 0..7  consumers: one 16-row x 32-column strip ("unit") of the panel each per round, DMMA from shared memory
-//   warp  8     producer : per K-chunk one cp.async.bulk for the panel's 32x32 B tile (shared by all consumers) and one
-//                          per active consumer for its 16x32 A strip, completing on the stage's `full` mbarrier
+//   warp  8     producer : per 16-wide K half-chunk one cp.async.bulk per active consumer for its 16x16 A piece and
+//                          two for the panel's 32x16 B piece (shared by all consumers), all completing on the stage's
+//                          `full` mbarrier; 4 stages of 20 KB
 //   warp  9     factor   : potrf + inverse of the 32x32 diagonal tile in registers while the consumers keep updating
 //
-// All consumers sweep K in lock step within a round (they share the B tile), the producer runs ahead across rounds and
-// panels, and the only cross-panel dependency -- tiles of block column j-1 written by panel j-1's triangular solves --
-// is the LAST chunk of every sweep, so the ring never drains at a panel boundary.  A strip is solved against L_jj^-1
-// straight out of registers when the inverse is already there, otherwise parked in its own slot of the factor and
-// solved at the end of the panel.
+// All consumers sweep K in lock step within a round (they share the B piece), the producer runs ahead across rounds
+// and panels, and the only cross-panel dependency -- tiles of block column j-1 written by panel j-1's triangular
+// solves -- is the LAST chunk of every sweep, so the ring rarely drains at a panel boundary.  A strip is solved against
+// L_jj^-1 straight out of registers when the inverse is already there, otherwise parked in its own slot of the factor
+// and solved at the end of the panel.
+//
+// Tile layout in the factor scratch and in the padded T tiles ("OF2"): [half h][ks][mi][lane],
+//   idx = (((h*8 + ks)*2 + mi)*32 + lane),  value = tile[h*16 + mi*8 + g][ks*4 + t]
+// so a 16-row strip is 4 KB contiguous and each of its K halves 2 KB contiguous (one bulk copy each).
 //
 // Generic-proxy stores of factor tiles are made visible to the async proxy (the bulk copies of later panels) by
 // fence.proxy.async before the arrive on `panel_done`.
@@ -20,11 +25,22 @@
 
 namespace bi {
 
+#ifndef PIPE_PREFETCH
+#define PIPE_PREFETCH 0   // L2 prefetch distance of the producer in 32-wide K chunks; measured: no gain (the ring is not DRAM-latency bound)
+#endif
+#ifndef PIPE_XBYTES
+#define PIPE_XBYTES (SUB_ELEMS * 8)   // experiment knob: bytes actually copied per A piece
+#endif
 constexpr int PIPE_CONSUMERS = 8;
 constexpr int PIPE_THREADS = (PIPE_CONSUMERS + 2) * 32;   // + producer + factor warp
-constexpr int PIPE_STAGES = 2;
+constexpr int PIPE_STAGES = 4;
 constexpr int STRIP_ELEMS = TILE_ELEMS / 2;                // 16 x 32 doubles = 4 KB
-constexpr int STAGE_ELEMS = TILE_ELEMS + PIPE_CONSUMERS * STRIP_ELEMS;   // B tile + 8 A strips = 40 KB
+constexpr int SUB_ELEMS = STRIP_ELEMS / 2;                 // 16 x 16 doubles = 2 KB: one K half of a strip
+constexpr int STAGE_ELEMS = 2 * SUB_ELEMS + PIPE_CONSUMERS * SUB_ELEMS;   // B piece (2 strips) + 8 A pieces = 20 KB
+
+__host__ __device__ __forceinline__ int of2_index(int r, int c) {
+    return ((((r >> 4) * 8 + (c >> 2)) * 2 + ((r >> 3) & 1)) << 5) + ((r & 7) << 2) + (c & 3);
+}
 
 __host__ __device__ inline size_t pipe_smem_bytes(int Fp, int K0p) {
     size_t b = 0;
@@ -32,12 +48,14 @@ __host__ __device__ inline size_t pipe_smem_bytes(int Fp, int K0p) {
     b += sizeof(double) * TILE_ELEMS;          // sLinv
     b += sizeof(double) * 32 * 33;             // sD
     b += sizeof(double) * 32;                  // sRinv
+    b += sizeof(double) * 256;                 // sLinvB
     b += sizeof(double) * (size_t)Fp;          // sDy
     b += sizeof(double) * (size_t)K0p * 2;     // sNegV, sM
     b += sizeof(double) * 16;                  // sRed (8) + logdet + spare
     b += sizeof(unsigned long long) * 16;      // mbarriers
     b += sizeof(int) * (size_t)Fp;             // sObs
     b += sizeof(int) * 8;                      // flags
+    b += sizeof(int) * 4 * (size_t)(Fp / 32);  // kmin, imax, tile_omin, tile_omax
     return b + 128;                            // alignment slack
 }
 
@@ -52,7 +70,7 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
 __device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ bool mbar_test(unsigned long long* bar, uint32_t parity) {
+__device__ __forceinline__ bool mbar_try(unsigned long long* bar, uint32_t parity) {   // may suspend for a while
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -63,8 +81,19 @@ __device__ __forceinline__ bool mbar_test(unsigned long long* bar, uint32_t pari
         : "memory");
     return ok != 0;
 }
+__device__ __forceinline__ bool mbar_test(unsigned long long* bar, uint32_t parity) {  // never blocks
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
-    while (!mbar_test(bar, parity)) {
+    while (!mbar_try(bar, parity)) {
     }
 }
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
@@ -72,16 +101,186 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
 struct PipeParams {
     CholParams c;
-    const double* TmP;   // T tiles padded to whole 32-wide K chunks: [nt][nTc][1024] operand-fragment-major
+    const double* TmP;   // T tiles padded to whole 32-wide K chunks: [nt][nTc][1024], OF2 layout
     int nTc;             // number of 32-wide chunks of T (ceil(K0 / 32)); K0p = 32 * nTc
+    long long* dbg;      // developer timing buffer (PIPE_TIMING builds only), else nullptr
 };
+
+#ifdef PIPE_TIMING
+#define TSTART() long long t0_ = clock64()
+#define TADD(cat) do { long long t1_ = clock64(); tacc[cat] += t1_ - t0_; t0_ = t1_; } while (0)
+#else
+#define TSTART()
+#define TADD(cat)
+#endif
 
 // mbarrier slots
 enum { BAR_FULL = 0, BAR_EMPTY = PIPE_STAGES, BAR_DIAG = 2 * PIPE_STAGES, BAR_LINV, BAR_PANEL, BAR_COUNT };
+
+// 32 DMMAs of one K half-chunk: A piece [ks4][mi][lane], B piece [h][ks4][mi][lane]
+template <bool SCALE>
+__device__ __forceinline__ void half_chunk_mma(double (&acc)[2][4][2], const double* As, const double* Bs, const double* nv4) {
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+        double a[2], b[4];
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi) a[mi] = As[(ks * 2 + mi) * 32];
+#pragma unroll
+        for (int nf = 0; nf < 4; ++nf) {
+            b[nf] = Bs[(((nf >> 1) * 4 + ks) * 2 + (nf & 1)) * 32];
+            if (SCALE) b[nf] *= nv4[4 * ks];
+        }
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+            for (int nf = 0; nf < 4; ++nf) dmma(acc[mi][nf], a[mi], b[nf]);
+    }
+}
+
+// X = C L_jj^-T for one 16 x 32 strip held as operand fragments a[mi][ks]; sLinv is [nf][ks][lane]
+__device__ __forceinline__ void strip_trsm(const double (&a)[2][8], double (&x)[2][4][2], const double* sLinvLane) {
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+        for (int nf = 0; nf < 4; ++nf) x[mi][nf][0] = x[mi][nf][1] = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks)
+#pragma unroll
+        for (int nf = 0; nf < 4; ++nf)
+            if (ks <= 2 * nf + 1) {   // L^-1 is lower triangular
+                const double b = sLinvLane[(nf * 8 + ks) * 32];
+#pragma unroll
+                for (int mi = 0; mi < 2; ++mi) dmma(x[mi][nf], a[mi][ks], b);
+            }
+}
+
+// ---- diagonal tile: blocked factorisation by one warp ------------------------------------------------------------------
+// The FP64 tensor pipe is shared with the consumers' DMMAs, so what counts here is the NUMBER of FP64 instructions the
+// factor warp issues, not only their dependency chain.  The 32 x 32 tile is factorised in 4 block columns of 8:
+// lane r holds row r of the 32 x 8 panel, 8 right-looking scalar steps factor the diagonal block and solve the panel
+// below it at once, and the trailing update L_panel L_panel^T goes through DMMA.  No 32 x 32 inverse is formed: the
+// consumers' triangular solve is blocked too and only needs L_jj and the four 8 x 8 inverses of its diagonal blocks.
+//   sD     32 x 33 row-major: in C_jj (lower), out L_jj (lower)
+//   sLjj   [nf][ks][lane] operand-fragment-major L_jj (B operand of the blocked solve), upper part zero
+//   sLinvB [b][kk][lane]: (L_bb)^-1 of the four 8 x 8 diagonal blocks as B fragments
+// returns 0 or the 1-based index of the first non-positive pivot; adds sum(log L_ii) to logdet.
+__device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, double* sLinvB, double* sRinv, int lane, double& logdet) {
+    const int g = lane >> 2, t = lane & 3;
+    int bad = 0;
+    double mypiv = 1.0;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        double a[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) a[c] = sD[lane * 33 + 8 * b + c];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const double p = shfl_d(a[c], 8 * b + c);
+            if (!(p > 0.0) && bad == 0) bad = 8 * b + c + 1;
+            if (lane == 8 * b + c) mypiv = p;
+            const double rinv = rsqrt(p);
+            a[c] *= rinv;                       // rows below the pivot: L[r][8b+c]; the pivot row: sqrt(p)
+            if (lane == 8 * b + c) sRinv[8 * b + c] = rinv;
+#pragma unroll
+            for (int c2 = c + 1; c2 < 8; ++c2) {
+                const double l = shfl_d(a[c], 8 * b + c2);
+                a[c2] = fma(-a[c], l, a[c2]);
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+            if (lane >= 8 * b + c) sD[lane * 33 + 8 * b + c] = a[c];
+        __syncwarp();
+        // trailing update: T[8mf.., 8nf..] -= L[8mf.., 8b..8b+7] L[8nf.., 8b..8b+7]^T   for b < nf <= mf <= 3
+#pragma unroll
+        for (int mf = b + 1; mf < 4; ++mf) {
+            double am[2];
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk) am[kk] = -sD[(8 * mf + g) * 33 + 8 * b + 4 * kk + t];
+#pragma unroll
+            for (int nf = b + 1; nf <= mf; ++nf) {
+                double cacc[2];
+                cacc[0] = sD[(8 * mf + g) * 33 + 8 * nf + 2 * t];
+                cacc[1] = sD[(8 * mf + g) * 33 + 8 * nf + 2 * t + 1];
+#pragma unroll
+                for (int kk = 0; kk < 2; ++kk) dmma(cacc, am[kk], sD[(8 * nf + g) * 33 + 8 * b + 4 * kk + t]);
+                sD[(8 * mf + g) * 33 + 8 * nf + 2 * t] = cacc[0];
+                sD[(8 * mf + g) * 33 + 8 * nf + 2 * t + 1] = cacc[1];
+            }
+        }
+        __syncwarp();
+    }
+    if (bad) return bad;
+    logdet += warp_sum(0.5 * log(mypiv));
+    // (L_bb)^-1: lane 8b + c computes column c of block b by forward substitution on the identity
+    {
+        const int b = lane >> 3, c = lane & 7;
+        double x[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            double s = 0.0;
+#pragma unroll
+            for (int k = 0; k < r; ++k) s = fma(sD[(8 * b + r) * 33 + 8 * b + k], x[k], s);
+            x[r] = ((r == c ? 1.0 : 0.0) - s) * sRinv[8 * b + r];
+        }
+#pragma unroll
+        for (int n = 0; n < 8; ++n) sLinvB[(b * 2 + (c >> 2)) * 32 + n * 4 + (c & 3)] = x[n];
+    }
+    // L_jj as B operand
+#pragma unroll 4
+    for (int idx = lane; idx < TILE_ELEMS; idx += 32) {
+        const int nf = idx >> 8, ks = (idx >> 5) & 7;
+        const int n = 8 * nf + g, k = 4 * ks + t;
+        sLjj[idx] = (k <= n) ? sD[n * 33 + k] : 0.0;
+    }
+    return 0;
+}
+
+// one accumulator fragment (8 rows x 8 columns) -> its two operand fragments (k-slices of 4 columns)
+__device__ __forceinline__ void cfrag_to_of2(const double (&c)[2], double& a0, double& a1, int lane) {
+    const int base = lane & 28, hi = (lane & 3) >> 1;
+    const double v00 = shfl_d(c[0], base | hi), v01 = shfl_d(c[1], base | hi);
+    const double v10 = shfl_d(c[0], base | 2 | hi), v11 = shfl_d(c[1], base | 2 | hi);
+    a0 = (lane & 1) ? v01 : v00;
+    a1 = (lane & 1) ? v11 : v10;
+}
+
+// Blocked triangular solve X = C L_jj^-T of one 16 x 32 strip, in place: c[mi][nf] (accumulator fragments) -> X as
+// accumulator fragments, xa[mi][ks] the same X as operand fragments.  sLjjLane / sLinvBLane already offset by lane.
+__device__ __forceinline__ void strip_trsm_blocked(double (&c)[2][4][2], double (&xa)[2][8], const double* sLjjLane,
+                                                   const double* sLinvBLane, int lane) {
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        // t = sum_{a<b} X_a L_{b,a}^T
+        double tacc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+        for (int ks = 0; ks < 2 * b; ++ks) {
+            const double bl = sLjjLane[(b * 8 + ks) * 32];
+#pragma unroll
+            for (int mi = 0; mi < 2; ++mi) dmma(tacc[mi], xa[mi][ks], bl);
+        }
+        const double i0 = sLinvBLane[(b * 2) * 32], i1 = sLinvBLane[(b * 2 + 1) * 32];
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi) {
+            double sfrag[2] = {c[mi][b][0] - tacc[mi][0], c[mi][b][1] - tacc[mi][1]};
+            double s0, s1;
+            cfrag_to_of2(sfrag, s0, s1, lane);
+            double x[2] = {0.0, 0.0};
+            dmma(x, s0, i0);
+            dmma(x, s1, i1);
+            c[mi][b][0] = x[0];
+            c[mi][b][1] = x[1];
+            cfrag_to_of2(x, xa[mi][2 * b], xa[mi][2 * b + 1], lane);
+        }
+    }
+}
 
 template <bool EXPLICIT>
 __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipeParams PP) {
@@ -91,7 +290,8 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
     double* sLinv = sStage + (size_t)PIPE_STAGES * STAGE_ELEMS;
     double* sD = sLinv + TILE_ELEMS;
     double* sRinv = sD + 32 * 33;
-    double* sDy = sRinv + 32;
+    double* sLinvB = sRinv + 32;
+    double* sDy = sLinvB + 256;
     const int K0p = PP.nTc * 32;
     double* sNegV = sDy + P.Fp;
     double* sM = sNegV + K0p;
@@ -99,6 +299,10 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(sRed + 16);
     int* sObs = reinterpret_cast<int*>(bars + 16);
     int* sFlag = sObs + P.Fp;
+    int* sKmin = sFlag + 8;
+    int* sImax = sKmin + P.nt;
+    int* sOmin = sImax + P.nt;
+    int* sOmax = sOmin + P.nt;
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
@@ -123,9 +327,15 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
     }
     if (!EXPLICIT)
         for (int r = tid; r < P.Fp; r += PIPE_THREADS) sObs[r] = P.obs_id[r];
+    for (int r = tid; r < P.nt; r += PIPE_THREADS) {
+        sKmin[r] = P.kmin[r];
+        sImax[r] = P.imax[r];
+        sOmin[r] = EXPLICIT ? 0 : P.tile_omin[r];
+        sOmax[r] = EXPLICIT ? 0 : P.tile_omax[r];
+    }
     __syncthreads();
 
-    uint32_t it = 0;       // K-chunks issued / consumed so far (identical sequence in producer and consumers)
+    uint32_t it = 0;       // K half-chunks issued / consumed so far (identical sequence in producer and consumers)
     uint32_t gpanel = 0;   // panels processed so far by this CTA (parity of the per-panel barriers)
 
     for (long long w = blockIdx.x; w < P.W; w += gridDim.x) {
@@ -169,91 +379,104 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
 
         if (warp == PIPE_CONSUMERS) {
             // =============================== producer ==========================================================
-            if (lane == 0) {
-                uint32_t gp = gpanel;
-                for (int j = 0; j < nt; ++j, ++gp) {
-                    const int i_hi = P.imax[j];
-                    const int nreg = 2 * (i_hi - j + 1);
-                    const int nunits = nreg + 1;
-                    bool waited = false;
-                    for (int r0 = 0; r0 < nunits; r0 += PIPE_CONSUMERS) {
-                        const int nact = min(PIPE_CONSUMERS, nunits - r0);
-                        const bool first_z = (r0 == nreg);
-                        const int i_first = first_z ? nt : j + (r0 >> 1);
-                        // ---- T chunks (theta-dependent part of the covariance)
-                        if (!EXPLICIT && !first_z && P.tile_omax[j] >= P.tile_omin[i_first]) {
-                            for (int c = 0; c < nTc; ++c, ++it) {
-                                const int s = it % PIPE_STAGES;
-                                mbar_wait(&bars[BAR_EMPTY + s], ((it / PIPE_STAGES) & 1) ^ 1);
-                                double* st = sStage + (size_t)s * STAGE_ELEMS;
-                                int nstrip = 0;
-                                for (int u = 0; u < nact; ++u) {
-                                    const int q = r0 + u;
-                                    if (q == nreg) break;
-                                    const int i = j + (q >> 1);
-                                    if (P.tile_omax[j] >= P.tile_omin[i]) ++nstrip;
-                                }
-                                mbar_expect_tx(&bars[BAR_FULL + s], (uint32_t)((TILE_ELEMS + nstrip * STRIP_ELEMS) * 8));
-                                bulk_g2s(st, PP.TmP + ((size_t)j * nTc + c) * TILE_ELEMS, TILE_ELEMS * 8, &bars[BAR_FULL + s]);
-                                for (int u = 0; u < nact; ++u) {
-                                    const int q = r0 + u;
-                                    if (q == nreg) break;
-                                    const int i = j + (q >> 1);
-                                    if (P.tile_omax[j] >= P.tile_omin[i])
-                                        bulk_g2s(st + TILE_ELEMS + u * STRIP_ELEMS,
-                                                 PP.TmP + ((size_t)i * nTc + c) * TILE_ELEMS + (q & 1) * STRIP_ELEMS,
-                                                 STRIP_ELEMS * 8, &bars[BAR_FULL + s]);
-                                }
-                            }
-                        }
-                        // ---- factor chunks k < j
-                        const bool z_in_round = nreg < r0 + PIPE_CONSUMERS;
-                        const int klo = P.kmin[z_in_round ? j : i_first];
-                        for (int k = klo; k < j; ++k, ++it) {
-                            if (k == j - 1 && !waited) {
-                                // block column j-1 was written by panel j-1's solves: wait for all of them
-                                mbar_wait(&bars[BAR_PANEL], (gp - 1) & 1);
-                                waited = true;
-                            }
+            // lane u < 8 owns the A piece of the round's u-th unit, lanes 8 and 9 the two halves of the shared B piece,
+            // lane 0 arms the barrier
+            uint32_t gp = gpanel;
+            for (int j = 0; j < nt; ++j, ++gp) {
+                const int i_hi = sImax[j];
+                const int nreg = 2 * (i_hi - j + 1);
+                const int nunits = nreg + 1;
+                const double* Bsrc = wsL + (size_t)j * (j - 1) / 2 * TILE_ELEMS;
+                const int bh = lane - PIPE_CONSUMERS;   // 0 / 1 on the B lanes
+                bool waited = false;
+                for (int r0 = 0; r0 < nunits; r0 += PIPE_CONSUMERS) {
+                    const int nact = min(PIPE_CONSUMERS, nunits - r0);
+                    const bool first_z = (r0 == nreg);
+                    const int i_first = first_z ? nt : j + (r0 >> 1);
+                    const int q = r0 + lane;
+                    const bool has = lane < nact;
+                    const bool uz = has && (q == nreg);
+                    const int i = uz ? nt : j + (q >> 1);
+                    const int my_kmin = has ? sKmin[uz ? j : i] : 0x7fffffff;
+                    const bool my_need0 = !EXPLICIT && has && !uz && sOmax[j] >= sOmin[min(i, nt - 1)];
+                    // ---- T chunks (theta-dependent part of the covariance)
+                    if (!EXPLICIT && !first_z && sOmax[j] >= sOmin[i_first]) {
+                        const uint32_t bytes = (uint32_t)((2 + __popc(__ballot_sync(0xffffffffu, my_need0))) * SUB_ELEMS * 8);
+                        const double* Asrc = PP.TmP + (size_t)min(i, nt - 1) * nTc * TILE_ELEMS + (q & 1) * STRIP_ELEMS;
+                        const double* Bt = PP.TmP + (size_t)j * nTc * TILE_ELEMS;
+                        for (int c2 = 0; c2 < 2 * nTc; ++c2, ++it) {
                             const int s = it % PIPE_STAGES;
                             mbar_wait(&bars[BAR_EMPTY + s], ((it / PIPE_STAGES) & 1) ^ 1);
                             double* st = sStage + (size_t)s * STAGE_ELEMS;
-                            int nstrip = 0;
-                            for (int u = 0; u < nact; ++u) {
-                                const int q = r0 + u;
-                                const int km = P.kmin[(q == nreg) ? j : j + (q >> 1)];
-                                if (k >= km) ++nstrip;
-                            }
-                            mbar_expect_tx(&bars[BAR_FULL + s], (uint32_t)((TILE_ELEMS + nstrip * STRIP_ELEMS) * 8));
-                            bulk_g2s(st, wsL + ((size_t)j * (j - 1) / 2 + k) * TILE_ELEMS, TILE_ELEMS * 8, &bars[BAR_FULL + s]);
-                            for (int u = 0; u < nact; ++u) {
-                                const int q = r0 + u;
-                                const bool uz = (q == nreg);
-                                const int i = uz ? nt : j + (q >> 1);
-                                if (k < P.kmin[uz ? j : i]) continue;
-                                const double* src = uz ? wsZ + (size_t)k * TILE_ELEMS
-                                                       : wsL + ((size_t)i * (i - 1) / 2 + k) * TILE_ELEMS + (q & 1) * STRIP_ELEMS;
-                                bulk_g2s(st + TILE_ELEMS + u * STRIP_ELEMS, src, STRIP_ELEMS * 8, &bars[BAR_FULL + s]);
-                            }
+                            const size_t off = (size_t)(c2 >> 1) * TILE_ELEMS + (c2 & 1) * SUB_ELEMS;
+                            if (lane == 0) mbar_expect_tx(&bars[BAR_FULL + s], bytes);
+                            __syncwarp();
+                            if (my_need0) bulk_g2s(st + (2 + lane) * SUB_ELEMS, Asrc + off, SUB_ELEMS * 8, &bars[BAR_FULL + s]);
+                            if (bh == 0 || bh == 1)
+                                bulk_g2s(st + bh * SUB_ELEMS, Bt + off + bh * STRIP_ELEMS, SUB_ELEMS * 8, &bars[BAR_FULL + s]);
                         }
                     }
-                    // every phase of BAR_PANEL is observed exactly once, in order (parity waits must not skip a phase)
-                    if (!waited && gp > 0) mbar_wait(&bars[BAR_PANEL], (gp - 1) & 1);
+                    // ---- factor chunks k < j
+                    const bool z_in_round = nreg < r0 + PIPE_CONSUMERS;
+                    const int klo = sKmin[z_in_round ? j : i_first];
+                    const double* Asrc = uz ? wsZ : wsL + (size_t)i * (i - 1) / 2 * TILE_ELEMS + (q & 1) * STRIP_ELEMS;
+#if PIPE_PREFETCH > 0
+                    // pull the first chunks of this sweep into L2 (the factor of 296 walkers does not fit there)
+                    for (int k = klo; k < min(j, klo + PIPE_PREFETCH); ++k) {
+                        if (k >= my_kmin) bulk_prefetch_l2(Asrc + (size_t)k * TILE_ELEMS, STRIP_ELEMS * 8);
+                        if (bh == 0 || bh == 1) bulk_prefetch_l2(Bsrc + (size_t)k * TILE_ELEMS + bh * STRIP_ELEMS, STRIP_ELEMS * 8);
+                    }
+#endif
+                    for (int k = klo; k < j; ++k) {
+#if PIPE_PREFETCH > 0
+                        if (k + PIPE_PREFETCH < j) {
+                            if (k + PIPE_PREFETCH >= my_kmin) bulk_prefetch_l2(Asrc + (size_t)(k + PIPE_PREFETCH) * TILE_ELEMS, STRIP_ELEMS * 8);
+                            if (bh == 0 || bh == 1)
+                                bulk_prefetch_l2(Bsrc + (size_t)(k + PIPE_PREFETCH) * TILE_ELEMS + bh * STRIP_ELEMS, STRIP_ELEMS * 8);
+                        }
+#endif
+                        if (k == j - 1 && !waited) {
+                            // block column j-1 was written by panel j-1's solves: wait for all of them
+                            mbar_wait(&bars[BAR_PANEL], (gp - 1) & 1);
+                            waited = true;
+                        }
+                        const bool part = k >= my_kmin;
+                        const uint32_t bytes = (uint32_t)(2 * SUB_ELEMS * 8 + __popc(__ballot_sync(0xffffffffu, part)) * PIPE_XBYTES);
+                        for (int kh = 0; kh < 2; ++kh, ++it) {
+                            const int s = it % PIPE_STAGES;
+                            mbar_wait(&bars[BAR_EMPTY + s], ((it / PIPE_STAGES) & 1) ^ 1);
+                            double* st = sStage + (size_t)s * STAGE_ELEMS;
+                            const size_t off = (size_t)k * TILE_ELEMS + kh * SUB_ELEMS;
+                            if (lane == 0) mbar_expect_tx(&bars[BAR_FULL + s], bytes);
+                            __syncwarp();
+                            if (part) bulk_g2s(st + (2 + lane) * SUB_ELEMS, Asrc + off, PIPE_XBYTES, &bars[BAR_FULL + s]);
+                            if (bh == 0 || bh == 1)
+                                bulk_g2s(st + bh * SUB_ELEMS, Bsrc + off + bh * STRIP_ELEMS, SUB_ELEMS * 8, &bars[BAR_FULL + s]);
+                        }
+                    }
                 }
+                // every phase of BAR_PANEL is observed exactly once, in order (parity waits must not skip a phase)
+                if (!waited && gp > 0) mbar_wait(&bars[BAR_PANEL], (gp - 1) & 1);
             }
-            __syncwarp();
         } else if (warp == PIPE_CONSUMERS + 1) {
             // =============================== factor warp ========================================================
             double logdet = 0.0;
             int first_bad = 0;
             uint32_t gp = gpanel;
+#ifdef PIPE_TIMING
+            long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#endif
+            TSTART();
             for (int j = 0; j < nt; ++j, ++gp) {
                 mbar_wait(&bars[BAR_DIAG], gp & 1);
-                const int bad = warp_potrf_inv(sD, sLinv, sRinv, lane, logdet);
+                TADD(7);
+                const int bad = warp_potrf_blocked(sD, sLinv, sLinvB, sRinv, lane, logdet);
+                TADD(6);
                 if (bad) {
                     if (first_bad == 0) first_bad = j * 32 + bad;
                     // keep the data flow alive (control flow must not depend on the data): poison the inverse
                     for (int n = 0; n < 32; ++n) sLinv[n * 32 + lane] = __longlong_as_double(0x7ff8000000000000LL);
+                    for (int n = 0; n < 8; ++n) sLinvB[n * 32 + lane] = __longlong_as_double(0x7ff8000000000000LL);
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bars[BAR_LINV]);
@@ -262,16 +485,26 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                 sRed[8] = logdet;
                 sFlag[1] = first_bad;
             }
+#ifdef PIPE_TIMING
+            if (PP.dbg && lane == 0) {
+                atomicAdd((unsigned long long*)&PP.dbg[6], (unsigned long long)tacc[6]);
+                atomicAdd((unsigned long long*)&PP.dbg[7], (unsigned long long)tacc[7]);
+            }
+#endif
         } else {
             // =============================== consumers ==========================================================
             double zpart = 0.0;
             uint32_t gp = gpanel;
+#ifdef PIPE_TIMING
+            long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#endif
+            TSTART();
             for (int j = 0; j < nt; ++j, ++gp) {
-                const int i_hi = P.imax[j];
+                const int i_hi = sImax[j];
                 const int nreg = 2 * (i_hi - j + 1);
                 const int nunits = nreg + 1;
-                const int omin_j = EXPLICIT ? 0 : P.tile_omin[j];
-                const int omax_j = EXPLICIT ? 0 : P.tile_omax[j];
+                const int omin_j = sOmin[j];
+                const int omax_j = sOmax[j];
                 uint32_t deferred = 0;
                 int rnd = 0;
                 for (int r0 = 0; r0 < nunits; r0 += PIPE_CONSUMERS, ++rnd) {
@@ -288,32 +521,21 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
 #pragma unroll
                         for (int nf = 0; nf < 4; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
 
-                    if (!EXPLICIT && !first_z && omax_j >= P.tile_omin[i_first]) {
-                        const bool need0 = active && !is_z && omax_j >= P.tile_omin[i];
-                        for (int c = 0; c < nTc; ++c, ++it) {
+                    if (!EXPLICIT && !first_z && omax_j >= sOmin[i_first]) {
+                        const bool need0 = active && !is_z && omax_j >= sOmin[i];
+                        for (int c2 = 0; c2 < 2 * nTc; ++c2, ++it) {
                             const int s = it % PIPE_STAGES;
                             mbar_wait(&bars[BAR_FULL + s], (it / PIPE_STAGES) & 1);
+                            TADD(0);
                             if (need0) {
                                 const double* Bs = sStage + (size_t)s * STAGE_ELEMS + lane;
-                                const double* As = Bs + TILE_ELEMS + warp * STRIP_ELEMS;
-#pragma unroll
-                                for (int ks = 0; ks < 8; ++ks) {
-                                    const double nv = sNegV[c * 32 + 4 * ks + t];
-                                    double a[2], b[4];
-#pragma unroll
-                                    for (int mi = 0; mi < 2; ++mi) a[mi] = As[(mi * 8 + ks) * 32];
-#pragma unroll
-                                    for (int nf = 0; nf < 4; ++nf) b[nf] = Bs[(nf * 8 + ks) * 32] * nv;
-#pragma unroll
-                                    for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-                                        for (int nf = 0; nf < 4; ++nf) dmma(acc[mi][nf], a[mi], b[nf]);
-                                }
+                                half_chunk_mma<true>(acc, Bs + (2 + warp) * SUB_ELEMS, Bs, sNegV + c2 * 16 + t);
                             }
                             __syncwarp();
                             if (lane == 0) mbar_arrive(&bars[BAR_EMPTY + s]);
+                            TADD(1);
                         }
-                        if (need0 && omin_j != P.tile_omax[i]) {
+                        if (need0 && omin_j != sOmax[i]) {
 #pragma unroll
                             for (int mi = 0; mi < 2; ++mi) {
                                 const int orow = sObs[i * 32 + (2 * h + mi) * 8 + g];
@@ -327,32 +549,22 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                     }
                     {
                         const bool z_in_round = nreg < r0 + PIPE_CONSUMERS;
-                        const int klo = P.kmin[z_in_round ? j : i_first];
-                        const int my_klo = active ? P.kmin[is_z ? j : i] : 0x7fffffff;
-                        for (int k = klo; k < j; ++k, ++it) {
+                        const int klo = sKmin[z_in_round ? j : i_first];
+                        const int my_klo = active ? sKmin[is_z ? j : i] : 0x7fffffff;
+                        for (int k2 = 2 * klo; k2 < 2 * j; ++k2, ++it) {
                             const int s = it % PIPE_STAGES;
                             mbar_wait(&bars[BAR_FULL + s], (it / PIPE_STAGES) & 1);
-                            if (k >= my_klo) {
+                            TADD(0);
+                            if ((k2 >> 1) >= my_klo) {
                                 const double* Bs = sStage + (size_t)s * STAGE_ELEMS + lane;
-                                const double* As = Bs + TILE_ELEMS + warp * STRIP_ELEMS;
-#pragma unroll
-                                for (int ks = 0; ks < 8; ++ks) {
-                                    double a[2], b[4];
-#pragma unroll
-                                    for (int mi = 0; mi < 2; ++mi) a[mi] = As[(mi * 8 + ks) * 32];
-#pragma unroll
-                                    for (int nf = 0; nf < 4; ++nf) b[nf] = Bs[(nf * 8 + ks) * 32];
-#pragma unroll
-                                    for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-                                        for (int nf = 0; nf < 4; ++nf) dmma(acc[mi][nf], a[mi], b[nf]);
-                                }
+                                half_chunk_mma<false>(acc, Bs + (2 + warp) * SUB_ELEMS, Bs, nullptr);
                             }
                             __syncwarp();
                             if (lane == 0) mbar_arrive(&bars[BAR_EMPTY + s]);
+                            TADD(1);
                         }
                     }
-                    if (!active) continue;
+                    if (!active) { TADD(2); continue; }
                     // ---- C = A_ij - acc
                     if (is_z) {
 #pragma unroll
@@ -398,99 +610,84 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                                 for (int e = 0; e < 2; ++e) sD[(h * 16 + mi * 8 + g) * 33 + nf * 8 + 2 * t + e] = acc[mi][nf][e];
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&bars[BAR_DIAG]);
+                        TADD(2);
                         continue;
                     }
                     double* Ct = (is_z ? wsZ + (long long)j * TILE_ELEMS : wsL + ((long long)i * (i - 1) / 2 + j) * TILE_ELEMS) +
                                  h * STRIP_ELEMS + lane;
-                    double a[2][8];
-#pragma unroll
-                    for (int mi = 0; mi < 2; ++mi) cf_to_of(acc[mi], a[mi], lane);
                     if (!mbar_test(&bars[BAR_LINV], gp & 1)) {
-                        // inverse not there yet: park the strip, solve at the end of the panel
-#pragma unroll
-                        for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-                            for (int ks = 0; ks < 8; ++ks) Ct[(mi * 8 + ks) * 32] = a[mi][ks];
-                        deferred |= 1u << rnd;
-                        continue;
-                    }
-                    // ---- triangular solve against the 32 x 32 inverse: X = C L_jj^-T
-#pragma unroll
-                    for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-                        for (int nf = 0; nf < 4; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
-#pragma unroll
-                    for (int ks = 0; ks < 8; ++ks)
-#pragma unroll
-                        for (int nf = 0; nf < 4; ++nf)
-                            if (ks <= 2 * nf + 1) {
-                                const double b = sLinv[(nf * 8 + ks) * 32 + lane];
-#pragma unroll
-                                for (int mi = 0; mi < 2; ++mi) dmma(acc[mi][nf], a[mi][ks], b);
-                            }
-                    if (is_z && g == 0) {
-#pragma unroll
-                        for (int nf = 0; nf < 4; ++nf) zpart += acc[0][nf][0] * acc[0][nf][0] + acc[0][nf][1] * acc[0][nf][1];
-                    }
-#pragma unroll
-                    for (int mi = 0; mi < 2; ++mi) {
-                        double a8[8];
-                        cf_to_of(acc[mi], a8, lane);
-#pragma unroll
-                        for (int ks = 0; ks < 8; ++ks) Ct[(mi * 8 + ks) * 32] = a8[ks];
-                    }
-                }
-                // ---- deferred strips of this panel
-                if (deferred) {
-                    mbar_wait(&bars[BAR_LINV], gp & 1);
-                    for (int rr = 0; deferred >> rr; ++rr) {
-                        if (!((deferred >> rr) & 1)) continue;
-                        const int q = rr * PIPE_CONSUMERS + warp;
-                        const bool is_z = (q == nreg);
-                        const int i = is_z ? nt : j + (q >> 1);
-                        const int h = is_z ? 0 : (q & 1);
-                        double* Ct = (is_z ? wsZ + (long long)j * TILE_ELEMS : wsL + ((long long)i * (i - 1) / 2 + j) * TILE_ELEMS) +
-                                     h * STRIP_ELEMS + lane;
-                        double a[2][8];
-#pragma unroll
-                        for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-                            for (int ks = 0; ks < 8; ++ks) a[mi][ks] = Ct[(mi * 8 + ks) * 32];
-                        double x[2][4][2];
-#pragma unroll
-                        for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-                            for (int nf = 0; nf < 4; ++nf) x[mi][nf][0] = x[mi][nf][1] = 0.0;
-#pragma unroll
-                        for (int ks = 0; ks < 8; ++ks)
-#pragma unroll
-                            for (int nf = 0; nf < 4; ++nf)
-                                if (ks <= 2 * nf + 1) {
-                                    const double b = sLinv[(nf * 8 + ks) * 32 + lane];
-#pragma unroll
-                                    for (int mi = 0; mi < 2; ++mi) dmma(x[mi][nf], a[mi][ks], b);
-                                }
-                        if (is_z && g == 0) {
-#pragma unroll
-                            for (int nf = 0; nf < 4; ++nf) zpart += x[0][nf][0] * x[0][nf][0] + x[0][nf][1] * x[0][nf][1];
-                        }
+                        // factor of the diagonal tile not there yet: park the strip, solve at the end of the panel
 #pragma unroll
                         for (int mi = 0; mi < 2; ++mi) {
                             double a8[8];
-                            cf_to_of(x[mi], a8, lane);
+                            cf_to_of(acc[mi], a8, lane);
 #pragma unroll
-                            for (int ks = 0; ks < 8; ++ks) Ct[(mi * 8 + ks) * 32] = a8[ks];
+                            for (int ks = 0; ks < 8; ++ks) Ct[(ks * 2 + mi) * 32] = a8[ks];
                         }
+                        deferred |= 1u << rnd;
+                        TADD(2);
+                        continue;
                     }
-                } else {
-                    // every warp observes the phase so that the parity sequence stays aligned
-                    mbar_wait(&bars[BAR_LINV], gp & 1);
+                    {
+                        double xa[2][8];
+                        strip_trsm_blocked(acc, xa, sLinv + lane, sLinvB + lane, lane);
+                        if (is_z && g == 0) {
+#pragma unroll
+                            for (int nf = 0; nf < 4; ++nf) zpart += acc[0][nf][0] * acc[0][nf][0] + acc[0][nf][1] * acc[0][nf][1];
+                        }
+#pragma unroll
+                        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                            for (int ks = 0; ks < 8; ++ks) Ct[(ks * 2 + mi) * 32] = xa[mi][ks];
+                    }
+                    TADD(3);
+                }
+                // ---- deferred strips of this panel (also: every warp observes every phase of BAR_LINV, in order)
+                mbar_wait(&bars[BAR_LINV], gp & 1);
+                TADD(4);
+                for (int rr = 0; rr < rnd; ++rr) {
+                    if (!((deferred >> rr) & 1)) continue;
+                    const int q = rr * PIPE_CONSUMERS + warp;
+                    const bool is_z = (q == nreg);
+                    const int i = is_z ? nt : j + (q >> 1);
+                    const int h = is_z ? 0 : (q & 1);
+                    double* Ct = (is_z ? wsZ + (long long)j * TILE_ELEMS : wsL + ((long long)i * (i - 1) / 2 + j) * TILE_ELEMS) +
+                                 h * STRIP_ELEMS + lane;
+                    // the strip was parked as operand fragments; rebuild its accumulator fragments (inverse quad shuffle)
+                    double x[2][4][2];
+#pragma unroll
+                    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                        for (int nf = 0; nf < 4; ++nf) {
+                            const double a0 = Ct[((2 * nf) * 2 + mi) * 32], a1 = Ct[((2 * nf + 1) * 2 + mi) * 32];
+                            // element (g, 2t+e) of the 8x8 block sits in operand fragment (2t+e)>>2 at lane (g, (2t+e)&3)
+                            const int t_ = lane & 3, base = lane & 28;
+                            const double p0 = shfl_d(a0, base | ((2 * t_) & 3)), p1 = shfl_d(a1, base | ((2 * t_) & 3));
+                            const double q0 = shfl_d(a0, base | ((2 * t_ + 1) & 3)), q1 = shfl_d(a1, base | ((2 * t_ + 1) & 3));
+                            x[mi][nf][0] = (t_ >= 2) ? p1 : p0;
+                            x[mi][nf][1] = (t_ >= 2) ? q1 : q0;
+                        }
+                    double xa[2][8];
+                    strip_trsm_blocked(x, xa, sLinv + lane, sLinvB + lane, lane);
+                    if (is_z && g == 0) {
+#pragma unroll
+                        for (int nf = 0; nf < 4; ++nf) zpart += x[0][nf][0] * x[0][nf][0] + x[0][nf][1] * x[0][nf][1];
+                    }
+#pragma unroll
+                    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                        for (int ks = 0; ks < 8; ++ks) Ct[(ks * 2 + mi) * 32] = xa[mi][ks];
                 }
                 // this panel's tiles -> visible to the async proxy (bulk copies of later panels)
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bars[BAR_PANEL]);
+                TADD(5);
             }
+#ifdef PIPE_TIMING
+            if (PP.dbg && lane == 0)
+                for (int c = 0; c < 8; ++c) atomicAdd((unsigned long long*)&PP.dbg[warp * 8 + c], (unsigned long long)tacc[c]);
+#endif
             const double zs = warp_sum(zpart);
             if (lane == 0) sRed[warp] = zs;
         }
