@@ -326,7 +326,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
             return bail(BI_E_ARG);
         }
         I.N = g.n_design; I.P = g.n_pc; I.Fg = g.n_features; I.R = g.n_rest;
-        I.nks = (I.N + 3) / 4; I.ntn = (I.N + 1 + 31) / 32; I.K0g = ((I.P + 3) / 4) * 4; I.pc_off = pc_off;
+        I.nks = ((I.N + 15) / 16) * 4; I.ntn = (I.N + 1 + 31) / 32; I.K0g = ((I.P + 3) / 4) * 4; I.pc_off = pc_off;
         pc_off += I.P;
         h->Nmax = std::max(h->Nmax, I.N);
         const int N = I.N, Pg = I.P, Fg = I.Fg;

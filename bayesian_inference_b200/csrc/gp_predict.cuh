@@ -23,7 +23,7 @@ struct PcDesc {
     const double* ell;     // (d)
     const double* LinvF;   // ntn tiles of (32 rows n) x (4*nks) in operand-fragment-major; row N = alpha
     int N;
-    int nks;               // ceil(N / 4)
+    int nks;               // ceil(N / 4) rounded up to a multiple of 4 (k-steps are consumed in groups of 4)
     int ntn;               // ceil((N + 1) / 32)
     int kind;
     double cst;            // ConstantKernel value
@@ -36,7 +36,7 @@ constexpr int GP_WT = 32;          // walkers per CTA
 constexpr int GP_THREADS = 256;
 
 __host__ __device__ inline size_t gp_smem_bytes(int d, int Nmax) {
-    const int nks = (Nmax + 3) / 4;
+    const int nks = ((Nmax + 15) / 16) * 4;   // K steps, padded to whole groups of 4
     size_t b = 0;
     b += sizeof(double) * (size_t)GP_WT * 4 * nks;   // sA  (32 walkers x 4*nks), operand-fragment-major
     b += sizeof(double) * (size_t)d * Nmax;          // sX
@@ -63,7 +63,7 @@ __device__ __forceinline__ double stationary_kernel(int kind, double sq) {
 // k_out (optional): (W, k_ld_pc, N) row-major slice for this group, PC index = desc.local.
 // m_out / v_out (optional): (W, Ptot) at column blockIdx.y + pc_first.
 template <bool DO_GP>
-__global__ void __launch_bounds__(GP_THREADS) gp_predict_kernel(const PcDesc* __restrict__ pcs, int pc_first, int d,
+__global__ void __launch_bounds__(GP_THREADS, 2) gp_predict_kernel(const PcDesc* __restrict__ pcs, int pc_first, int d,
                                                                 const double* __restrict__ theta, long long W,
                                                                 double* __restrict__ k_out, int k_npc,
                                                                 double* __restrict__ m_out, double* __restrict__ v_out,
@@ -112,45 +112,75 @@ __global__ void __launch_bounds__(GP_THREADS) gp_predict_kernel(const PcDesc* __
     __syncthreads();
 
     // ---- K2 -------------------------------------------------------------------------------------------------
+    // warp (wm, wn): walker rows wm*16.., n-tiles {t : snake(t) == wn}.  The B operand (rows of L^-1, L2 resident,
+    // shared by every CTA of this PC) is streamed global -> registers in groups of 4 k-steps, one group ahead of the
+    // DMMAs that consume it (the loads' L2 latency is what bounded the first version of this kernel).
     const int wm = warp & 1;    // rows wm*16 .. wm*16+15
     const int wn = warp >> 1;   // n-tile owner 0..3
     const int g = lane >> 2, t = lane & 3;
     double sumsq[2] = {0.0, 0.0};
     double meanv[2] = {0.0, 0.0};
     const double* sAw = sA + (size_t)(2 * wm) * nks * 32 + lane;
-    for (int nt_ = 0; nt_ < pc.ntn; ++nt_) {
-        const int slot = nt_ & 7;
-        if (((slot < 4) ? slot : 7 - slot) != wn) continue;     // snake assignment balances the triangle
-        const int klim = min(nks, 8 * (nt_ + 1));
-        const double* Bt = pc.LinvF + (size_t)nt_ * 4 * nks * 32 + lane;
-        double acc[2][4][2];
+    const size_t tile_stride = (size_t)4 * nks * 32;
+
+    auto tile_of = [&](int idx) {   // idx-th n-tile owned by this warp (snake order balances the triangle)
+        const int blk = idx >> 1;
+        return blk * 8 + ((idx & 1) ? 7 - wn : wn);
+    };
+    auto load_group = [&](double (&bb)[4][4], int tile, int grp) {
+        const double* Bt = pc.LinvF + (size_t)tile * tile_stride + (size_t)(grp * 4) * 32 + lane;
 #pragma unroll
-        for (int mi = 0; mi < 2; ++mi)
+        for (int kk = 0; kk < 4; ++kk)
 #pragma unroll
-            for (int nf = 0; nf < 4; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
-#pragma unroll 2
-        for (int ks = 0; ks < klim; ++ks) {
-            double a[2], b[4];
-#pragma unroll
-            for (int mi = 0; mi < 2; ++mi) a[mi] = sAw[(mi * nks + ks) * 32];
-#pragma unroll
-            for (int nf = 0; nf < 4; ++nf) b[nf] = __ldg(Bt + (nf * nks + ks) * 32);
+            for (int nf = 0; nf < 4; ++nf) bb[kk][nf] = __ldg(Bt + ((size_t)nf * nks + kk) * 32);
+    };
+
+    int idx = 0;
+    int tile = tile_of(0);
+    if (tile < pc.ntn) {
+        double bcur[4][4], bnxt[4][4];
+        load_group(bcur, tile, 0);
+        while (tile < pc.ntn) {
+            const int ngrp = min(nks, 8 * (tile + 1)) >> 2;   // nks is a multiple of 4
+            double acc[2][4][2];
 #pragma unroll
             for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
-                for (int nf = 0; nf < 4; ++nf) dmma(acc[mi][nf], a[mi], b[nf]);
-        }
+                for (int nf = 0; nf < 4; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
+            const int next_tile = tile_of(idx + 1);
+            for (int grp = 0; grp < ngrp; ++grp) {
+                // prefetch the next group (of this tile, or the first of the next tile)
+                if (grp + 1 < ngrp) load_group(bnxt, tile, grp + 1);
+                else if (next_tile < pc.ntn) load_group(bnxt, next_tile, 0);
 #pragma unroll
-        for (int mi = 0; mi < 2; ++mi)
+                for (int kk = 0; kk < 4; ++kk) {
+                    double a[2];
 #pragma unroll
-            for (int nf = 0; nf < 4; ++nf)
+                    for (int mi = 0; mi < 2; ++mi) a[mi] = sAw[(mi * nks + grp * 4 + kk) * 32];
 #pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const int n = nt_ * 32 + nf * 8 + 2 * t + e;
-                    const double x = acc[mi][nf][e];
-                    if (n < N) sumsq[mi] = fma(x, x, sumsq[mi]);
-                    else if (n == N) meanv[mi] = x;
+                    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                        for (int nf = 0; nf < 4; ++nf) dmma(acc[mi][nf], a[mi], bcur[kk][nf]);
                 }
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)
+#pragma unroll
+                    for (int nf = 0; nf < 4; ++nf) bcur[kk][nf] = bnxt[kk][nf];
+            }
+#pragma unroll
+            for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                for (int nf = 0; nf < 4; ++nf)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int n = tile * 32 + nf * 8 + 2 * t + e;
+                        const double x = acc[mi][nf][e];
+                        if (n < N) sumsq[mi] = fma(x, x, sumsq[mi]);
+                        else if (n == N) meanv[mi] = x;
+                    }
+            ++idx;
+            tile = next_tile;
+        }
     }
 #pragma unroll
     for (int mi = 0; mi < 2; ++mi) {
