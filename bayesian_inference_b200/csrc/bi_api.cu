@@ -17,6 +17,7 @@
 #include "cov_assemble.cuh"
 #include "gp_predict.cuh"
 #include "setup_kernels.cuh"
+#include "woodbury.cuh"
 
 using namespace bi;
 
@@ -49,6 +50,18 @@ struct bi_handle_s {
     int nTc = 0, chol_impl = 2;
     size_t pipe_smem = 0;
     double a_ndiv = -1.0;
+    // Woodbury mode (allocated on first use)
+    std::vector<std::array<long long, 4>> blk;   // observable blocks sorted by out_start: [group, out, in, len]
+    std::vector<WbBlock> wbBlocks;
+    WbBlock* dWbBlocks = nullptr;
+    int wbPmax = 0, wbNt = 0;
+    long long wbChunk = 0, wbStride = 0;
+    int wbCtas = 0;
+    size_t wbSmem = 0;
+    double wb_ndiv = -1.0;
+    double *dG = nullptr, *dH = nullptr, *dQ0 = nullptr, *dLdA = nullptr;
+    double *dMw = nullptr, *dUw = nullptr, *dQuadA = nullptr, *dQuadM = nullptr, *dLdM = nullptr, *dLpW = nullptr, *dWbWs = nullptr;
+    int *dInfoW = nullptr, *dWbK = nullptr;
     int *dObs = nullptr, *dTileOmin = nullptr, *dTileOmax = nullptr;
     int *dKminDense = nullptr, *dImaxDense = nullptr, *dKminStruct = nullptr, *dImaxStruct = nullptr;
     long long max_batch = 4096;
@@ -418,6 +431,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         for (int b = 0; b < h->B; ++b)
             for (int k = 0; k < 4; ++k) blocks[b][k] = D->blocks[(size_t)b * 4 + k];
         std::sort(blocks.begin(), blocks.end(), [](const auto& a, const auto& b) { return a[1] < b[1]; });
+        h->blk = blocks;
         for (int b = 0; b < h->B; ++b) {
             const long long gi = blocks[b][0], so = blocks[b][1], si = blocks[b][2], ln = blocks[b][3];
             if (gi < 0 || gi >= h->G || ln <= 0 || so < 0 || so + ln > F || si < 0 || si + ln > h->groups[gi].Fg) {
@@ -714,13 +728,128 @@ int bi_predict_host(bi_handle h, const double* theta, int64_t W, double n_div, d
     return predict_host(h, -1, theta, W, n_div, mean_out, cov_out);
 }
 
+// the explicit-matrix Cholesky kernel is shared by _loglikelihood and Woodbury: its opt-in smem limit only ever grows
+static cudaError_t raise_explicit_smem(size_t need) {
+    static size_t cur = 0;
+    if (need <= cur) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(chol_loglik_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
+    if (e == cudaSuccess) cur = need;
+    return e;
+}
+
+// ---- Woodbury mode ---------------------------------------------------------------------------------------------------
+static int ensure_woodbury(bi_handle h) {
+    if (h->dWbBlocks) return 0;
+    const int nB = (int)h->blk.size();
+    h->wbBlocks.resize(nB);
+    int Pmax = 0;
+    for (int b = 0; b < nB; ++b) Pmax = std::max(Pmax, h->groups[h->blk[b][0]].P);
+    if (Pmax > 64) return fail(h, BI_E_UNSUPPORTED, "Woodbury mode supports n_pc <= 64 per emulation group");
+    h->wbPmax = Pmax;
+    for (int b = 0; b < nB; ++b) {
+        const GroupImg& I = h->groups[h->blk[b][0]];
+        WbBlock& B = h->wbBlocks[b];
+        B.row0 = (int)h->blk[b][1]; B.f = (int)h->blk[b][3]; B.col0 = I.pc_off; B.P = I.P;
+        B.a_off = 0; B.y_off = 0; B.g_off = (long long)b * Pmax * Pmax;
+    }
+    int rc = upload(h, &h->dWbBlocks, h->wbBlocks.data(), h->wbBlocks.size());
+    if (rc) return rc;
+    if ((rc = dalloc(h, &h->dG, (size_t)nB * Pmax * Pmax))) return rc;
+    if ((rc = dalloc(h, &h->dH, (size_t)nB * Pmax))) return rc;
+    if ((rc = dalloc(h, &h->dQ0, (size_t)nB))) return rc;
+    if ((rc = dalloc(h, &h->dLdA, (size_t)nB))) return rc;
+    // per-call scratch: M matrices of a chunk of walkers
+    const long long per = (long long)nB * Pmax * Pmax * 8;
+    h->wbChunk = std::max<long long>(1, std::min<long long>(h->max_batch, (256ll << 20) / per));
+    const long long slots = h->wbChunk * nB;
+    if ((rc = dalloc(h, &h->dMw, (size_t)slots * Pmax * Pmax))) return rc;
+    if ((rc = dalloc(h, &h->dUw, (size_t)slots * Pmax))) return rc;
+    if ((rc = dalloc(h, &h->dQuadA, (size_t)slots))) return rc;
+    if ((rc = dalloc(h, &h->dQuadM, (size_t)slots))) return rc;
+    if ((rc = dalloc(h, &h->dLdM, (size_t)slots))) return rc;
+    if ((rc = dalloc(h, &h->dLpW, (size_t)slots))) return rc;
+    if ((rc = dalloc(h, &h->dInfoW, (size_t)slots))) return rc;
+    h->wbNt = (Pmax + 31) / 32;
+    std::vector<int> kd((size_t)2 * h->wbNt, 0);
+    for (int i = 0; i < h->wbNt; ++i) kd[(size_t)h->wbNt + i] = h->wbNt - 1;
+    if ((rc = upload(h, &h->dWbK, kd.data(), kd.size()))) return rc;
+    h->wbSmem = chol_smem_bytes(h->wbNt * 32, 4);
+    CK(raise_explicit_smem(h->wbSmem));
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_loglik_kernel<true>, CHOL_THREADS, h->wbSmem));
+    if (occ < 1) return fail(h, BI_E_UNSUPPORTED, "Woodbury: n_pc too large for the Cholesky kernel");
+    h->wbCtas = (int)std::min<long long>(slots, (long long)h->sm_count * occ);
+    h->wbStride = chol_ws_doubles(h->wbNt);
+    if ((rc = dalloc(h, &h->dWbWs, (size_t)h->wbCtas * h->wbStride))) return rc;
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+static int woodbury_setup(bi_handle h, double n_div, cudaStream_t s) {
+    if (h->wb_ndiv == n_div) return 0;
+    const int nB = (int)h->wbBlocks.size();
+    long long a_tot = 0, y_tot = 0;
+    for (int b = 0; b < nB; ++b) {
+        WbBlock& B = h->wbBlocks[b];
+        B.a_off = a_tot; B.y_off = y_tot;
+        a_tot += (long long)B.f * B.f; y_tot += (long long)B.f * (B.P + 1);
+    }
+    double *dA = nullptr, *dY = nullptr;
+    CK(cudaMalloc(&dA, (size_t)a_tot * 8));
+    CK(cudaMalloc(&dY, (size_t)y_tot * 8));
+    CK(cudaMemcpyAsync(h->dWbBlocks, h->wbBlocks.data(), sizeof(WbBlock) * nB, cudaMemcpyHostToDevice, s));
+    woodbury_setup_kernel<<<nB, 256, 0, s>>>(h->dWbBlocks, h->F, h->K0, h->wbPmax, h->dSig, h->dYerr, h->dUblk, n_div, h->dTrow,
+                                             h->dE, dA, dY, h->dG, h->dH, h->dQ0, h->dLdA);
+    h->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(dA); cudaFree(dY);
+    if (e != cudaSuccess) { h->err = std::string("woodbury_setup: ") + cudaGetErrorString(e); return (int)e; }
+    h->wb_ndiv = n_div;
+    return 0;
+}
+
+// theta, logp, info: device pointers; one pass of gp_predict + build + P x P Cholesky + combine per chunk of walkers
+static int run_woodbury(bi_handle h, const double* dTheta, long long W, double n_div, double* dLogp, int* dInfo, cudaStream_t s) {
+    int rc = ensure_woodbury(h);
+    if (rc) return rc;
+    if ((rc = woodbury_setup(h, n_div, s))) return rc;
+    const int nB = (int)h->wbBlocks.size(), Pm = h->wbPmax;
+    for (long long w0 = 0; w0 < W; w0 += h->wbChunk) {
+        const long long wb = std::min<long long>(h->wbChunk, W - w0);
+        if ((rc = launch_gp(h, dTheta + w0 * h->d, wb, h->dM, h->dV, s))) return rc;
+        woodbury_build_kernel<<<dim3(nB, (unsigned)wb), 64, 0, s>>>(h->dWbBlocks, nB, Pm, h->Ptot, h->dM, h->dV, h->dG, h->dH, h->dQ0,
+                                                                     h->dMw, h->dUw, h->dQuadA);
+        h->launches++;
+        CK(cudaGetLastError());
+        CholParams P;
+        std::memset(&P, 0, sizeof(P));
+        const long long slots = wb * nB;
+        P.F = Pm; P.Fp = h->wbNt * 32; P.nt = h->wbNt; P.K0 = 4; P.nks0 = 1; P.d = h->d; P.W = slots;
+        P.kmin = h->dWbK; P.imax = h->dWbK + h->wbNt; P.ws = h->dWbWs; P.ws_stride = h->wbStride;
+        P.logp = h->dLpW; P.info = h->dInfoW; P.cov_x = h->dMw; P.dy_x = h->dUw; P.quad_out = h->dQuadM; P.logdet_out = h->dLdM;
+        {
+            ProfScope ps(h, 1, s);
+            chol_loglik_kernel<true><<<(int)std::min<long long>(slots, h->wbCtas), CHOL_THREADS, h->wbSmem, s>>>(P);
+        }
+        h->launches++;
+        CK(cudaGetLastError());
+        woodbury_combine_kernel<<<(unsigned)((wb + 127) / 128), 128, 0, s>>>(nB, wb, h->d, dTheta + w0 * h->d, h->dMin, h->dMax, h->dQuadA,
+                                                                             h->dQuadM, h->dLdM, h->dLdA, h->dInfoW, dLogp + w0,
+                                                                             dInfo ? dInfo + w0 : nullptr);
+        h->launches++;
+        CK(cudaGetLastError());
+    }
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 static int check_lp(bi_handle h, const double* theta, int64_t W, int mode, double* logp_out) {
     if (!h || !theta || !logp_out || W < 0) return fail(h, BI_E_ARG, "bad argument");
     if (!h->has_data) return fail(h, BI_E_STATE, "handle was created without experimental data");
-    if (mode != BI_MODE_DENSE && mode != BI_MODE_STRUCTURED) return fail(h, BI_E_UNSUPPORTED, "mode not implemented");
-    if (mode == BI_MODE_STRUCTURED && !h->sigma_blockdiag)
-        return fail(h, BI_E_STRUCTURE, "Sigma_exp couples observable blocks: structured mode is not valid");
+    if (mode != BI_MODE_DENSE && mode != BI_MODE_STRUCTURED && mode != BI_MODE_WOODBURY) return fail(h, BI_E_ARG, "unknown mode");
+    if (mode != BI_MODE_DENSE && !h->sigma_blockdiag)
+        return fail(h, BI_E_STRUCTURE, "Sigma_exp couples observable blocks: structured / Woodbury mode is not valid");
     return 0;
 }
 
@@ -741,6 +870,7 @@ int bi_log_posterior(bi_handle h, const double* theta, int64_t W, double n_div, 
         CK(cudaStreamSynchronize(s));
         n_div = cnt > 0 ? (double)cnt : 1.0;
     }
+    if (mode == BI_MODE_WOODBURY) return run_woodbury(h, theta, W, n_div, logp_out, info_out, s);
     rc = build_a_tiles(h, n_div, s);
     if (rc) return rc;
     for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
@@ -771,15 +901,22 @@ int bi_log_posterior_host(bi_handle h, const double* theta, int64_t W, double n_
         }
         n_div = cnt > 0 ? (double)cnt : 1.0;
     }
-    rc = build_a_tiles(h, n_div, h->stream);
-    if (rc) return rc;
+    if (mode != BI_MODE_WOODBURY) {
+        rc = build_a_tiles(h, n_div, h->stream);
+        if (rc) return rc;
+    }
     for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
         const long long wb = std::min<long long>(h->max_batch, W - w0);
         CK(cudaMemcpyAsync(h->dTheta, theta + w0 * h->d, (size_t)wb * h->d * 8, cudaMemcpyHostToDevice, h->stream));
-        rc = launch_gp(h, h->dTheta, wb, h->dM, h->dV, h->stream);
-        if (rc) return rc;
-        rc = launch_chol(h, h->dTheta, h->dM, h->dV, wb, mode, h->dLogp, h->dInfo, h->stream);
-        if (rc) return rc;
+        if (mode == BI_MODE_WOODBURY) {
+            rc = run_woodbury(h, h->dTheta, wb, n_div, h->dLogp, h->dInfo, h->stream);
+            if (rc) return rc;
+        } else {
+            rc = launch_gp(h, h->dTheta, wb, h->dM, h->dV, h->stream);
+            if (rc) return rc;
+            rc = launch_chol(h, h->dTheta, h->dM, h->dV, wb, mode, h->dLogp, h->dInfo, h->stream);
+            if (rc) return rc;
+        }
         CK(cudaMemcpyAsync(logp_out + w0, h->dLogp, (size_t)wb * 8, cudaMemcpyDeviceToHost, h->stream));
         if (info_out) CK(cudaMemcpyAsync(info_out + w0, h->dInfo, (size_t)wb * 4, cudaMemcpyDeviceToHost, h->stream));
         CK(cudaStreamSynchronize(h->stream));
@@ -794,7 +931,7 @@ int bi_loglikelihood_host(bi_handle h, const double* dy, const double* cov, int6
     CK(cudaSetDevice(h->device));
     const int F = Fdim, nt = (F + 31) / 32, Fp = nt * 32;
     const size_t smem = chol_smem_bytes(Fp, 4);
-    CK(cudaFuncSetAttribute(chol_loglik_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(raise_explicit_smem(smem));
     int occ = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_loglik_kernel<true>, CHOL_THREADS, smem));
     if (occ < 1) return fail(h, BI_E_UNSUPPORTED, "matrix too large for the Cholesky kernel's shared memory");

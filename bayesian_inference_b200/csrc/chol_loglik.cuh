@@ -49,6 +49,8 @@ struct CholParams {
     // EXPLICIT instantiation only (log_posterior._loglikelihood(y, cov), log_posterior.py:104):
     const double* cov_x;      // (W, F, F) row-major, lower triangle read
     const double* dy_x;       // (W, F)
+    double* quad_out;         // optional (W): dy^T C^-1 dy on its own (Woodbury combine), else nullptr
+    double* logdet_out;       // optional (W): sum log diag chol(C)
 };
 
 #ifndef CHOL_MIN_BLOCKS
@@ -395,11 +397,16 @@ __global__ void __launch_bounds__(CHOL_THREADS, CHOL_MIN_BLOCKS) chol_loglik_ker
         if (tid == 0) {
             if (failed) {
                 P.logp[w] = __longlong_as_double(0x7ff8000000000000LL);
+                if (EXPLICIT && P.quad_out) P.quad_out[w] = P.logdet_out[w] = __longlong_as_double(0x7ff8000000000000LL);
                 if (P.info) P.info[w] = sFlag[1] > P.F ? P.F : sFlag[1];
             } else {
                 double tot = 0.0;
                 for (int k = 0; k < CHOL_WARPS; ++k) tot += sRed[k];
                 P.logp[w] = -0.5 * tot - logdet;
+                if (EXPLICIT && P.quad_out) {
+                    P.quad_out[w] = tot;
+                    P.logdet_out[w] = logdet;
+                }
                 if (P.info) P.info[w] = 0;
             }
         }

@@ -160,7 +160,7 @@ def main() -> None:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3A")
     ap.add_argument("--walkers", type=int, default=0, help="walkers per GPU per step (default: the configuration's)")
-    ap.add_argument("--mode", default="dense", choices=["dense", "structured"])
+    ap.add_argument("--mode", default="dense", choices=["dense", "structured", "woodbury"])
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

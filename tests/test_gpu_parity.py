@@ -69,6 +69,8 @@ def test_golden_log_posterior(golden):
         _cmp_logp(rows, ref["ref_logp_rows"])
         if name != "toy_dense_sigma":
             _cmp_logp(dev.log_posterior(ref["theta"], n_div=1.0, mode="structured"), ref["ref_logp_rows"])
+            _cmp_logp(dev.log_posterior(ref["theta"], n_div=1.0, mode="woodbury"), ref["ref_logp_rows"])
+            _cmp_logp(dev.log_posterior(ref["theta"], n_div=None, mode="woodbury"), ref["ref_logp_batch"])
 
 
 def test_structured_mode_refused_when_sigma_couples_observables():
@@ -81,6 +83,8 @@ def test_structured_mode_refused_when_sigma_couples_observables():
     with _dev(z) as dev:
         with pytest.raises(DeviceError):
             dev.log_posterior(ref["theta"], mode="structured")
+        with pytest.raises(DeviceError):
+            dev.log_posterior(ref["theta"], mode="woodbury")
         want = cf.log_posterior(z, ref["theta"], n_div=1.0)
         _cmp_logp(dev.log_posterior(ref["theta"], mode="dense"), want)
 
@@ -113,6 +117,7 @@ def test_generated_config_vs_oracle(name, n_check, over):
         _cmp_logp(dev.log_posterior(th, n_div=1.0), want)
         if a.sigma_exp is None:
             _cmp_logp(dev.log_posterior(th, n_div=1.0, mode="structured"), want)
+            _cmp_logp(dev.log_posterior(th, n_div=1.0, mode="woodbury"), want)
 
 
 # ---- size-independent properties at the full BASELINE size ----------------------------------------------------------
@@ -141,12 +146,13 @@ def test_full_size_batch_equals_rows_and_is_deterministic(c3a):
     assert np.count_nonzero(np.isneginf(full)) == np.count_nonzero(~np.all((a.theta > a.min) & (a.theta < a.max), axis=1))
 
 
-def test_full_size_dense_equals_structured(c3a):
+def test_full_size_dense_equals_structured_equals_woodbury(c3a):
     a, _, dev = c3a
     d = dev.log_posterior(a.theta, n_div=1.0, mode="dense")
-    s = dev.log_posterior(a.theta, n_div=1.0, mode="structured")
     fin = np.isfinite(d)
-    assert np.array_equal(np.isneginf(d), np.isneginf(s)) and rel_err(s[fin], d[fin]) < TOL_LOGP
+    for mode in ("structured", "woodbury"):
+        s = dev.log_posterior(a.theta, n_div=1.0, mode=mode)
+        assert np.array_equal(np.isneginf(d), np.isneginf(s)) and rel_err(s[fin], d[fin]) < TOL_LOGP
 
 
 def test_full_size_torch_device_path_matches_host_path(c3a):

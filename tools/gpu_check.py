@@ -53,8 +53,8 @@ def check(name: str, n_check: int = 24, **over):
               f"{np.linalg.norm(cg - cgo) / np.linalg.norm(cgo):.3e}")
     # K4
     ref = cf.log_posterior(z, th, n_div=1.0)
-    for mode in ("dense", "structured"):
-        if mode == "structured" and a.sigma_exp is not None:
+    for mode in ("dense", "structured", "woodbury"):
+        if mode != "dense" and a.sigma_exp is not None:
             continue
         lp, info = dev.log_posterior(th, n_div=1.0, mode=mode, return_info=True)
         fin = np.isfinite(ref)
@@ -67,8 +67,8 @@ def check(name: str, n_check: int = 24, **over):
     print(f"  logp sample {ref[:3]}")
     # timing
     W = a.theta.shape[0]
-    for mode in ("dense", "structured"):
-        if mode == "structured" and a.sigma_exp is not None:
+    for mode in ("dense", "structured", "woodbury"):
+        if mode != "dense" and a.sigma_exp is not None:
             continue
         dev.log_posterior(a.theta[:min(W, 512)], mode=mode)
         t0 = time.time()
