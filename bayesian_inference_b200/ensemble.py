@@ -1,0 +1,181 @@
+"""Affine-invariant ensemble sampler (Goodman & Weare stretch move) -- the caller of the hot path.
+
+The reference drives ``log_posterior`` with ``emcee.EnsembleSampler`` (mcmc.py:83-107, emcee 3.1.4, pdm.lock:504).
+emcee is a third-party dependency that is not vendored in the reference and not installed in this image, so the
+sampler is restated here from the published algorithm and emcee 3.1.4's documented behaviour:
+
+* one ``numpy.random.RandomState`` drives everything, consumed per step in emcee's order: move selection (one uniform
+  draw), the red/blue split ``arange(W) % 2`` shuffled, then for each half ``rand(n)`` (stretch factors),
+  ``randint(n_other, size=n)`` (partners), the log-probability of the proposals, and ``rand()`` per walker (accept);
+* stretch factor ``zz = ((a-1) u + 1)^2 / a`` with ``a = 2``; proposal ``c - (c - s) zz``; accept when
+  ``(ndim-1) log zz + logp_new - logp_old > log u``;
+* NaN log-probability raises ``ValueError('Probability function returned NaN')``; ``-inf`` is allowed.
+
+What changes with respect to the reference's use of emcee: the log-probability callback is *vectorised* -- called once
+per half-step with all W/2 proposals (one C-ABI call, optionally sharded over GPUs by ``ShardedLogProb``) instead of
+once per walker through a ``multiprocessing`` pool.  With ``log_posterior.log_posterior_walkers`` as the callback every
+row is evaluated exactly as the reference evaluates a single walker, so the chain is the one emcee would produce from
+the same RandomState.
+
+Parity status: **unpinned against emcee itself** (not installable here); pinned against an independent scalar
+re-implementation in tests/test_ensemble.py, and the GPU-vs-oracle chain identity is tested under this same driver.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional
+
+import numpy as np
+
+
+class StretchEnsemble:
+    """Minimal stand-in for ``emcee.EnsembleSampler`` with the default ``StretchMove(a=2)``, vectorised callback."""
+
+    def __init__(self, nwalkers: int, ndim: int, log_prob_fn: Callable[[np.ndarray], np.ndarray], a: float = 2.0,
+                 seed: Optional[int] = None, random_state: Optional[np.random.RandomState] = None):
+        if nwalkers % 2:
+            raise ValueError("the red/blue stretch move needs an even number of walkers")
+        if nwalkers < 2 * ndim:
+            raise ValueError("It is unadvisable to use a red-blue move with fewer walkers than twice the number of dimensions.")
+        self.nwalkers, self.ndim, self.a = int(nwalkers), int(ndim), float(a)
+        self.log_prob_fn = log_prob_fn
+        self._random = random_state if random_state is not None else np.random.RandomState(seed)
+        self.n_log_prob_calls = 0
+        self.n_log_prob_rows = 0
+        self.reset()
+
+    # ---- storage (emcee backend subset used by mcmc.run_mcmc, mcmc.py:99-116) ---------------------------------
+    def reset(self) -> None:
+        self._chain: list[np.ndarray] = []
+        self._log_prob: list[np.ndarray] = []
+        self._accepted = np.zeros(self.nwalkers)
+        self.iteration = 0
+
+    def get_chain(self, flat: bool = False, discard: int = 0, thin: int = 1) -> np.ndarray:
+        c = np.asarray(self._chain).reshape(-1, self.nwalkers, self.ndim)[discard::thin]
+        return c.reshape(-1, self.ndim) if flat else c
+
+    def get_log_prob(self, flat: bool = False, discard: int = 0, thin: int = 1) -> np.ndarray:
+        lp = np.asarray(self._log_prob).reshape(-1, self.nwalkers)[discard::thin]
+        return lp.reshape(-1) if flat else lp
+
+    @property
+    def flatchain(self) -> np.ndarray:
+        return self.get_chain(flat=True)
+
+    @property
+    def flatlnprobability(self) -> np.ndarray:
+        return self.get_log_prob(flat=True)
+
+    @property
+    def acceptance_fraction(self) -> np.ndarray:
+        return self._accepted / max(self.iteration, 1)
+
+    def get_autocorr_time(self, c: float = 5.0, tol: float = 50.0) -> np.ndarray:
+        """Integrated autocorrelation time per parameter (Sokal window, as emcee.autocorr.integrated_time)."""
+        x = self.get_chain()
+        n_t, n_w, n_d = x.shape
+        tau = np.empty(n_d)
+        for d in range(n_d):
+            f = np.zeros(n_t)
+            for k in range(n_w):
+                y = x[:, k, d] - np.mean(x[:, k, d])
+                n = 1 << int(np.ceil(np.log2(max(2 * n_t, 2))))
+                ft = np.fft.fft(y, n=n)
+                acf = np.fft.ifft(ft * np.conjugate(ft))[:n_t].real
+                f += acf / acf[0] if acf[0] != 0 else 0.0
+            f /= n_w
+            taus = 2.0 * np.cumsum(f) - 1.0
+            m = np.arange(len(taus)) < c * taus
+            window = int(np.argmin(m)) if np.any(~m) else len(taus) - 1
+            tau[d] = taus[window]
+        if np.any(tol * tau > n_t):
+            raise RuntimeError(f"The chain is shorter than {tol} times the integrated autocorrelation time "
+                               f"for {int(np.sum(tol * tau > n_t))} parameter(s). Use this estimate with caution: tau = {tau}")
+        return tau
+
+    # ---- sampling -----------------------------------------------------------------------------------------------
+    def compute_log_prob(self, coords: np.ndarray) -> np.ndarray:
+        lp = np.asarray(self.log_prob_fn(np.ascontiguousarray(coords)), dtype=np.float64).reshape(-1)
+        self.n_log_prob_calls += 1
+        self.n_log_prob_rows += coords.shape[0]
+        if lp.shape[0] != coords.shape[0]:
+            raise ValueError("incompatible input dimensions")
+        if np.any(np.isnan(lp)):
+            raise ValueError("Probability function returned NaN")
+        return lp
+
+    def sample(self, initial_state: np.ndarray, iterations: int = 1, log_prob0: Optional[np.ndarray] = None):
+        coords = np.array(initial_state, dtype=np.float64, copy=True)
+        if coords.shape != (self.nwalkers, self.ndim):
+            raise ValueError("incompatible input dimensions")
+        if np.linalg.cond(np.cov(coords, rowvar=False).reshape(self.ndim, self.ndim)) > 1e8:
+            raise ValueError("Initial state has a large condition number. Make sure that your walkers are linearly independent.")
+        log_prob = self.compute_log_prob(coords) if log_prob0 is None else np.array(log_prob0, dtype=np.float64, copy=True)
+        rng = self._random
+        W, nd = self.nwalkers, self.ndim
+        all_inds = np.arange(W)
+        for _ in range(iterations):
+            rng.random_sample()                  # emcee: move = random.choice(moves, p=weights) -> one uniform draw
+            inds = all_inds % 2
+            rng.shuffle(inds)
+            for split in range(2):
+                S1 = inds == split
+                s, c = coords[S1], coords[~S1]
+                ns, nc = s.shape[0], c.shape[0]
+                zz = ((self.a - 1.0) * rng.rand(ns) + 1.0) ** 2.0 / self.a
+                factors = (nd - 1.0) * np.log(zz)
+                rint = rng.randint(nc, size=(ns,))
+                q = c[rint] - (c[rint] - s) * zz[:, None]
+                new_lp = self.compute_log_prob(q)
+                lnpdiff = factors + new_lp - log_prob[S1]
+                accept = lnpdiff > np.log(rng.rand(ns))
+                idx = all_inds[S1][accept]
+                coords[idx] = q[accept]
+                log_prob[idx] = new_lp[accept]
+                self._accepted[idx] += 1
+            self.iteration += 1
+            self._chain.append(coords.copy())
+            self._log_prob.append(log_prob.copy())
+            yield coords, log_prob
+
+    def run_mcmc(self, initial_state, nsteps: int, n_logging_steps: int = 100, logger=None, **kwargs):
+        """As LoggingEnsembleSampler.run_mcmc (mcmc.py:194-204): returns the last (coords, log_prob)."""
+        result = None
+        for n, result in enumerate(self.sample(initial_state, iterations=nsteps, **kwargs), start=1):
+            if logger is not None and (n % n_logging_steps == 0 or n == nsteps):
+                af = self.acceptance_fraction
+                logger.info(f"  step {n}: acceptance fraction: mean {af.mean()}, std {af.std()}, min {af.min()}, max {af.max()}")
+        return result
+
+
+class ShardedLogProb:
+    """Walker sharding over ranks: each rank evaluates a contiguous slice of the rows, one all-gather of
+    the log-probabilities closes the call.  Every rank runs the identical sampler (same seed), so proposals and
+    accept/reject are replicated and the all-gather is the only collective."""
+
+    def __init__(self, local_fn: Callable[[np.ndarray], np.ndarray], group=None):
+        import torch.distributed as dist
+
+        self.fn, self.dist, self.group = local_fn, dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.cuda = dist.get_backend(group) == "nccl"
+
+    @staticmethod
+    def bounds(n: int, world: int, rank: int) -> tuple[int, int]:
+        per = (n + world - 1) // world
+        return min(n, rank * per), min(n, (rank + 1) * per)
+
+    def __call__(self, X: np.ndarray) -> np.ndarray:
+        import torch
+
+        n = X.shape[0]
+        lo, hi = self.bounds(n, self.world, self.rank)
+        per = (n + self.world - 1) // self.world
+        local = np.full(per, np.nan)
+        if hi > lo:
+            local[:hi - lo] = self.fn(X[lo:hi])
+        dev = torch.device("cuda", torch.cuda.current_device()) if self.cuda else torch.device("cpu")
+        send = torch.from_numpy(local).to(dev)
+        recv = torch.empty(per * self.world, dtype=torch.float64, device=dev)
+        self.dist.all_gather_into_tensor(recv, send, group=self.group)
+        return recv.cpu().numpy()[:n]   # rank r's rows sit at [r*per, r*per + count): contiguous in row order

@@ -1,0 +1,129 @@
+"""Drop-in for the reference's ``bayesian_inference.mcmc.run_mcmc`` (mcmc.py:34-134) on the B200 log-posterior path.
+
+Same sequence as the reference: random start in the prior box -> first half of burn-in -> re-seed the walkers at the
+``n_walkers`` best distinct log-probabilities of the chain (mcmc.py:99) -> second half of burn-in -> production ->
+``mcmc.h5`` with the keys ``chain, acceptance_fraction, log_prob, autocorrelation_time[, design_point,
+experimental_pseudodata]`` (mcmc.py:111-125).
+
+Differences, all forced by what is (not) installed here or by the move to the GPU:
+* no ``multiprocessing`` pool: ``initialize_pool_variables`` loads the emulators into HBM once and the sampler calls
+  ``log_posterior_walkers`` once per half-step for all proposals (``StretchEnsemble``, a restatement of emcee's stretch
+  move; emcee itself is not installed in this image);
+* with ``torch.distributed`` initialised (one process per GPU) the proposals are sharded over the ranks and one
+  all-gather of log-probabilities closes each half-step;
+* ``seed`` makes the run reproducible (the reference never seeds, mcmc.py:88);
+* configuration / emulator / data loading is the reference's own code (out of scope): pass the loaded
+  objects in, or leave them ``None`` to have them loaded through the reference package if it is importable;
+* without silx/h5py the result dictionary is written as ``mcmc.npz`` next to where ``mcmc.h5`` would go.
+"""
+from __future__ import annotations
+
+import logging
+import os
+import pickle
+from typing import Any, Optional
+
+import numpy as np
+
+from . import log_posterior
+from .ensemble import ShardedLogProb, StretchEnsemble
+
+logger = logging.getLogger(__name__)
+
+
+def _write_results(output_dict: dict[str, Any], config) -> str:
+    out_dir = getattr(config, "mcmc_output_dir", None) or getattr(config, "output_dir", ".")
+    os.makedirs(out_dir, exist_ok=True)
+    try:
+        from bayesian_inference import data_IO  # the reference's writer, when its dependencies exist
+
+        data_IO.write_dict_to_h5(output_dict, out_dir, "mcmc.h5", verbose=True)
+        return os.path.join(out_dir, "mcmc.h5")
+    except Exception:
+        path = os.path.join(out_dir, "mcmc.npz")
+        flat = {}
+        for k, v in output_dict.items():
+            if isinstance(v, dict):
+                for kk, vv in v.items():
+                    flat[f"{k}/{kk}"] = np.asarray(vv)
+            elif v is not None:
+                flat[k] = np.asarray(v)
+        np.savez(path, **flat)
+        return path
+
+
+def run_mcmc(config, closure_index: int = -1, *, emulation_config=None, emulation_results=None,
+             experimental_results=None, design_point=None, seed: Optional[int] = None, mode: str = "dense",
+             sigma_exp: Optional[np.ndarray] = None, write: bool = True) -> dict[str, Any]:
+    """Run burn-in + production and return (and write) the reference's output dictionary."""
+    par = config.analysis_config["parameterization"][config.parameterization]
+    names, lo, hi = par["names"], np.asarray(par["min"], dtype=np.float64), np.asarray(par["max"], dtype=np.float64)
+    ndim = len(names)
+
+    if emulation_config is None or emulation_results is None or experimental_results is None:
+        from bayesian_inference import data_IO, emulation as ref_emulation   # reference package (training / I/O side)
+
+        emulation_config = ref_emulation.EmulationConfig.from_config_file(
+            analysis_name=config.analysis_name, parameterization=config.parameterization,
+            analysis_config=config.analysis_config, config_file=config.config_file)
+        emulation_results = emulation_config.read_all_emulator_groups()
+        experimental_results = data_IO.data_array_from_h5(config.output_dir, "observables.h5", pseudodata_index=closure_index,
+                                                          observable_filter=emulation_config.observable_filter)
+        if closure_index >= 0:
+            design_point = data_IO.design_array_from_h5(config.output_dir, filename="observables.h5", validation_set=True)[closure_index]
+
+    try:
+        import torch.distributed as dist
+
+        distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+    except Exception:
+        distributed = False
+
+    log_posterior.initialize_pool_variables(lo, hi, emulation_config, emulation_results, experimental_results, None,
+                                            sigma_exp=sigma_exp, mode=mode)
+    fn = log_posterior.log_posterior_walkers
+    if distributed:
+        fn = ShardedLogProb(fn)
+    rng = np.random.RandomState(seed)
+    sampler = StretchEnsemble(config.n_walkers, ndim, fn, random_state=rng)
+
+    logger.info("Initializing sampler...")
+    random_pos = rng.uniform(lo, hi, (config.n_walkers, ndim))                       # mcmc.py:88
+    nburn0 = config.n_burn_steps // 2
+    logger.info("Starting initial burn-in...")
+    sampler.run_mcmc(random_pos, nburn0, n_logging_steps=config.n_logging_steps, logger=logger)
+    logger.info("Resampling walker positions...")
+    X0 = sampler.flatchain[np.unique(sampler.flatlnprobability, return_index=True)[1][-config.n_walkers:]]   # mcmc.py:99
+    sampler.reset()
+    X0 = sampler.run_mcmc(X0, config.n_burn_steps - nburn0, n_logging_steps=config.n_logging_steps, logger=logger)[0]
+    sampler.reset()
+    logger.info("Burn-in complete.")
+    logger.info("Starting production...")
+    sampler.run_mcmc(X0, config.n_sampling_steps, n_logging_steps=config.n_logging_steps, logger=logger)
+
+    output_dict: dict[str, Any] = {
+        "chain": sampler.get_chain(),
+        "acceptance_fraction": sampler.acceptance_fraction,
+        "log_prob": sampler.get_log_prob(),
+    }
+    try:
+        output_dict["autocorrelation_time"] = sampler.get_autocorr_time()
+    except Exception as e:   # as the reference: keep going (mcmc.py:116-119)
+        output_dict["autocorrelation_time"] = None
+        logger.info(f"Could not compute autocorrelation time: {str(e)}")
+    if closure_index >= 0:
+        output_dict["design_point"] = design_point
+        output_dict["experimental_pseudodata"] = experimental_results
+    rank0 = (not distributed) or dist.get_rank() == 0
+    if write and rank0:
+        path = _write_results(output_dict, config)
+        logger.info(f"Wrote {path}")
+        sampler_file = getattr(config, "sampler_outputfile", None)
+        if sampler_file:
+            os.makedirs(os.path.dirname(sampler_file) or ".", exist_ok=True)
+            with open(sampler_file, "wb") as f:
+                pickle.dump({"chain": output_dict["chain"], "log_prob": output_dict["log_prob"],
+                             "acceptance_fraction": output_dict["acceptance_fraction"]}, f)
+    output_dict["n_log_prob_rows"] = sampler.n_log_prob_rows
+    logger.info("Done.")
+    return output_dict

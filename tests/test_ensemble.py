@@ -1,0 +1,147 @@
+"""The stretch-move ensemble sampler and the walker sharding (CPU: gloo, world_size 2)."""
+from __future__ import annotations
+
+import os
+import socket
+import types
+
+import numpy as np
+import pytest
+from conftest import load_golden
+
+from bayesian_inference_b200.ensemble import ShardedLogProb, StretchEnsemble
+from oracle import closed_form as cf
+
+
+def _gauss(x):
+    return -0.5 * np.sum((x - 0.3) ** 2 / 0.04, axis=1)
+
+
+def _scalar_reference_chain(logp, x0, nsteps, seed, a=2.0):
+    """Independent restatement: per-walker Python loops, the same RandomState consumption order."""
+    rng = np.random.RandomState(seed)
+    x = x0.copy()
+    W, nd = x.shape
+    lp = np.array([logp(x[i:i + 1])[0] for i in range(W)])
+    out = []
+    for _ in range(nsteps):
+        rng.random_sample()
+        inds = np.arange(W) % 2
+        rng.shuffle(inds)
+        for split in (0, 1):
+            mine = [i for i in range(W) if inds[i] == split]
+            other = [i for i in range(W) if inds[i] != split]
+            u = rng.rand(len(mine))
+            partners = rng.randint(len(other), size=(len(mine),))
+            props, fac = [], []
+            for k, i in enumerate(mine):
+                zz = ((a - 1.0) * u[k] + 1.0) ** 2.0 / a
+                cpos = x[other[partners[k]]]
+                props.append(cpos - (cpos - x[i]) * zz)
+                fac.append((nd - 1.0) * np.log(zz))
+            new = [logp(p[None, :])[0] for p in props]
+            for k, i in enumerate(mine):          # snapshot semantics: proposals were built before any update
+                if fac[k] + new[k] - lp[i] > np.log(rng.rand()):
+                    x[i], lp[i] = props[k], new[k]
+        out.append(x.copy())
+    return np.asarray(out)
+
+
+def test_vectorised_sampler_equals_scalar_restatement():
+    rng = np.random.RandomState(1)
+    x0 = rng.uniform(0, 1, (12, 3))
+    s = StretchEnsemble(12, 3, _gauss, seed=77)
+    s.run_mcmc(x0, 60)
+    assert np.array_equal(s.get_chain(), _scalar_reference_chain(_gauss, x0, 60, 77))
+    assert s.get_chain().shape == (60, 12, 3) and s.get_log_prob().shape == (60, 12)
+    assert 0.1 < s.acceptance_fraction.mean() < 0.9
+    assert s.flatchain.shape == (720, 3) and s.flatlnprobability.shape == (720,)
+
+
+def test_sampler_contract():
+    with pytest.raises(ValueError):
+        StretchEnsemble(4, 3, _gauss)                      # fewer than 2*ndim walkers
+    s = StretchEnsemble(8, 2, lambda x: np.full(len(x), np.nan), seed=0)
+    with pytest.raises(ValueError, match="NaN"):
+        s.run_mcmc(np.random.RandomState(0).rand(8, 2), 1)
+    s = StretchEnsemble(8, 2, _gauss, seed=0)
+    with pytest.raises(ValueError, match="condition number"):
+        s.run_mcmc(np.ones((8, 2)), 1)
+    box = lambda x: np.where(np.all((x > 0) & (x < 1), axis=1), 0.0, -np.inf)   # noqa: E731
+    s = StretchEnsemble(20, 2, box, seed=3)
+    s.run_mcmc(np.random.RandomState(5).uniform(0.2, 0.8, (20, 2)), 200)
+    assert np.all((s.flatchain > 0) & (s.flatchain < 1))   # -inf proposals are never accepted
+    tau = StretchEnsemble(20, 2, _gauss, seed=3)
+    tau.run_mcmc(np.random.RandomState(5).uniform(0, 1, (20, 2)), 2000)
+    t = tau.get_autocorr_time(tol=0)
+    assert t.shape == (2,) and np.all(t > 1) and np.all(t < 200)
+
+
+def test_run_mcmc_driver_sequence(monkeypatch, tmp_path):
+    """mcmc.run_mcmc with the oracle standing in for the GPU: burn-in, re-seed at the best distinct points, production."""
+    from bayesian_inference_b200 import log_posterior, mcmc
+
+    z, _ = load_golden("toy")
+    monkeypatch.setattr(log_posterior, "initialize_pool_variables", lambda *a, **k: None)
+    monkeypatch.setattr(log_posterior, "log_posterior_walkers", lambda X: cf.log_posterior(z, X, n_div=1.0))
+    cfg = types.SimpleNamespace(
+        analysis_config={"parameterization": {"p": {"names": ["a", "b", "c"], "min": list(z["min"]), "max": list(z["max"])}}},
+        parameterization="p", analysis_name="toy", config_file="", output_dir=str(tmp_path), mcmc_output_dir=str(tmp_path),
+        n_walkers=8, n_burn_steps=6, n_sampling_steps=5, n_logging_steps=2, sampler_outputfile=str(tmp_path / "s.pkl"))
+    out = mcmc.run_mcmc(cfg, emulation_config=object(), emulation_results={}, experimental_results={}, seed=5)
+    assert out["chain"].shape == (5, 8, 3) and out["log_prob"].shape == (5, 8) and out["acceptance_fraction"].shape == (8,)
+    assert out["autocorrelation_time"] is None            # chain far too short: recorded as None, like the reference
+    assert out["n_log_prob_rows"] == (8 + 3 * 8) + (8 + 3 * 8) + (8 + 5 * 8)   # two burn-in halves + production, W rows per step
+    again = mcmc.run_mcmc(cfg, emulation_config=object(), emulation_results={}, experimental_results={}, seed=5, write=False)
+    assert np.array_equal(out["chain"], again["chain"])
+    assert (tmp_path / "mcmc.npz").exists() or (tmp_path / "mcmc.h5").exists()
+
+
+# ---- world_size-2 gloo: sharded log-probability and replicated sampler ------------------------------------------------
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        calls = []
+
+        def local(x):
+            calls.append(x.shape[0])
+            return _gauss(x)
+
+        fn = ShardedLogProb(local)
+        X = np.random.RandomState(0).rand(7, 3)           # ragged: 4 + 3
+        full = fn(X)
+        s = StretchEnsemble(10, 3, fn, seed=11)
+        s.run_mcmc(np.random.RandomState(2).rand(10, 3), 25)
+        q.put((rank, full, s.get_chain(), calls[0]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_logprob_gloo_world2():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
+    [p.join(60) for p in procs]
+    X = np.random.RandomState(0).rand(7, 3)
+    single = StretchEnsemble(10, 3, _gauss, seed=11)
+    single.run_mcmc(np.random.RandomState(2).rand(10, 3), 25)
+    for rank, full, chain, first_rows in res:
+        assert np.array_equal(full, _gauss(X))                       # gathered in row order, ragged tail handled
+        assert np.array_equal(chain, single.get_chain())             # every rank holds the same chain as 1 process
+        assert first_rows == (4 if rank == 0 else 3)                 # each rank evaluated only its slice
+    assert ShardedLogProb.bounds(7, 2, 0) == (0, 4) and ShardedLogProb.bounds(7, 2, 1) == (4, 7)
+    assert ShardedLogProb.bounds(2, 4, 3) == (2, 2)                  # more ranks than rows: empty slice
