@@ -300,6 +300,12 @@ def main() -> None:
     line = None
     if rank == 0:
         fl = dense_flops_per_eval(F, P)
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+                traffic = json.load(f).get(f"chol_pipe_kernel|{spec.name}|{W}|{args.mode}", {}).get("traffic_bytes")
+        except Exception:
+            pass
         ch_avg_s = ch_ms / max(ch_n, 1) * 1e-3
         achieved = fl * W / ch_avg_s / 1e12 if ch_n else None
         line = dict(base, value=value, ms_per_step=total_ms / args.steps,
@@ -308,9 +314,10 @@ def main() -> None:
                          "d2h_bytes_per_step": int(W * 12), "api": "log_posterior.log_posterior_walkers(numpy) -> numpy",
                          "matches_device_path": same},
                     gpu_launches=int(launches),
-                    roofline={"kernel": "chol_loglik_kernel (K4: assembly + Cholesky + solve + log-det)",
+                    roofline={"kernel": "chol_pipe_kernel (K4: assembly + Cholesky + solve + log-det)" if args.mode != "woodbury" else "chol_loglik_kernel<explicit> on P x P (Woodbury); flops counted as the dense path for comparability",
                               "bound": "tensor", "achieved": achieved, "peak": FP64_TENSOR_PEAK_TFLOPS, "unit": "TFLOP/s",
-                              "frac": (achieved / FP64_TENSOR_PEAK_TFLOPS) if achieved else None, "traffic": None,
+                              "frac": (achieved / FP64_TENSOR_PEAK_TFLOPS) if achieved else None, "traffic": traffic,
+                              "traffic_unit": "bytes per launch (dram read+write, ncu capture of the same command)",
                               "peak_source": "FP64 DMMA microbenchmark on this pool's B200 (profiles/r01_fp64_peak_microbench.txt); "
                                              "MEASURED_PEAKS.json holds no FP64 figure; cuBLAS DGEMM sustained = "
                                              f"{FP64_DGEMM_TFLOPS} TFLOP/s",
