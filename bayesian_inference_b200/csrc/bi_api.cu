@@ -72,6 +72,7 @@ struct bi_handle_s {
     int chol_ctas = 0;
     long long ws_stride = 0;
     size_t chol_smem = 0, gp_smem = 0;
+    int gp_wt = 32;
     double* dOutScratch = nullptr;   // staging for *_host outputs (mean / cov / k)
     size_t out_scratch_bytes = 0;
     long long launches = 0;
@@ -157,10 +158,27 @@ struct ProfScope {
 };
 
 int launch_gp(bi_handle h, const double* dTheta, long long W, double* dM, double* dV, cudaStream_t s) {
-    dim3 grid((unsigned)((W + GP_WT - 1) / GP_WT), (unsigned)h->Ptot);
+    const int wt = h->gp_wt;
+    dim3 grid((unsigned)((W + wt - 1) / wt), (unsigned)h->Ptot);
     {
         ProfScope ps(h, 0, s);
-        gp_predict_kernel<true><<<grid, GP_THREADS, h->gp_smem, s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
+#ifdef GP_TIMING
+        { unsigned long long z[8] = {0}; cudaMemcpyToSymbolAsync(gp_dbg, z, sizeof(z), 0, cudaMemcpyHostToDevice, s); }
+#endif
+        if (wt == 64)
+            gp_predict_kernel<true, 64><<<grid, 512, h->gp_smem, s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
+        else
+            gp_predict_kernel<true, 32><<<grid, 256, h->gp_smem, s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
+#ifdef GP_TIMING
+        {
+            unsigned long long z[8];
+            cudaMemcpyFromSymbolAsync(z, gp_dbg, sizeof(z), 0, cudaMemcpyDeviceToHost, s);
+            cudaStreamSynchronize(s);
+            const double nc = (double)grid.x * grid.y;
+            std::fprintf(stderr, "[gp timing] ctas %.0f: load %.0f  k1 %.0f  sync %.0f  k2 %.0f  reduce+sync %.0f cycles per CTA (thread 0)\n", nc,
+                         z[0] / nc, z[1] / nc, z[2] / nc, z[3] / nc, z[4] / nc);
+        }
+#endif
     }
     h->launches++;
     CK(cudaGetLastError());
@@ -543,13 +561,21 @@ int bi_create(const bi_desc* D, bi_handle* out) {
     TRY(dalloc(h, &h->dInfo, (size_t)mb));
     TRY(dalloc(h, &h->dCount, (size_t)1));
 
-    h->gp_smem = gp_smem_bytes(d, h->Nmax);
+    h->gp_wt = 32;   // measured (C3, B200): 32 walkers x 2 CTAs/SM 0.124 ms, 64 walkers x 1 CTA/SM 0.138 ms per 1024 walkers
+    if (const char* e = std::getenv("BI_GP_WT")) h->gp_wt = std::atoi(e) == 64 ? 64 : 32;   // developer A/B knob
+    if (gp_smem_bytes(d, h->Nmax, h->gp_wt) > 227 * 1024) h->gp_wt = 32;
+    h->gp_smem = gp_smem_bytes(d, h->Nmax, h->gp_wt);
     if (h->gp_smem > 227 * 1024) {
         h->err = "n_design too large for the GP kernel's shared-memory operand tile";
         return bail(BI_E_UNSUPPORTED);
     }
-    CKB(cudaFuncSetAttribute(gp_predict_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
-    CKB(cudaFuncSetAttribute(gp_predict_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
+    if (h->gp_wt == 64) {
+        CKB(cudaFuncSetAttribute(gp_predict_kernel<true, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
+        CKB(cudaFuncSetAttribute(gp_predict_kernel<false, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
+    } else {
+        CKB(cudaFuncSetAttribute(gp_predict_kernel<true, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
+        CKB(cudaFuncSetAttribute(gp_predict_kernel<false, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
+    }
     {
         const size_t cs = (size_t)(2 * 32 * (std::max(h->K0, 4) + 1) + std::max(h->K0, 4)) * sizeof(double);
         CKB(cudaFuncSetAttribute(cov_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(cs, 48 * 1024)));
@@ -592,9 +618,12 @@ int bi_kernel_vectors(bi_handle h, int group, const double* theta, int64_t W, do
     CK(cudaSetDevice(h->device));
     cudaStream_t s = (cudaStream_t)stream;
     const GroupImg& I = h->groups[group];
-    dim3 grid((unsigned)((W + GP_WT - 1) / GP_WT), (unsigned)I.P);
-    gp_predict_kernel<false><<<grid, GP_THREADS, h->gp_smem, s>>>(h->dPcs, I.pc_off, h->d, theta, W, k_out, I.P, nullptr,
-                                                                  nullptr, h->Ptot);
+    const int wt = h->gp_wt;
+    dim3 grid((unsigned)((W + wt - 1) / wt), (unsigned)I.P);
+    if (wt == 64)
+        gp_predict_kernel<false, 64><<<grid, 512, h->gp_smem, s>>>(h->dPcs, I.pc_off, h->d, theta, W, k_out, I.P, nullptr, nullptr, h->Ptot);
+    else
+        gp_predict_kernel<false, 32><<<grid, 256, h->gp_smem, s>>>(h->dPcs, I.pc_off, h->d, theta, W, k_out, I.P, nullptr, nullptr, h->Ptot);
     h->launches++;
     CK(cudaGetLastError());
     return 0;

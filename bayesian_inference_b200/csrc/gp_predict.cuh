@@ -13,6 +13,7 @@
 // operand-fragment-major layout (and, for bi_kernel_vectors, to HBM row-major).
 // K2: V = k L^-T as an FP64 DMMA contraction against L^-1 (computed once at load time), row n = N of the B operand
 // holds alpha so the mean falls out of the same product; sum V^2 is reduced in registers -> shuffles -> shared.
+// Only the lower triangle of L^-1 is multiplied, at the granularity of one 8-row fragment x one 4-column k-step.
 #pragma once
 #include "common.cuh"
 
@@ -32,10 +33,19 @@ struct PcDesc {
     int local;             // index of this PC inside its group
 };
 
-constexpr int GP_WT = 32;          // walkers per CTA
-constexpr int GP_THREADS = 256;
+#ifdef GP_TIMING
+__device__ unsigned long long gp_dbg[8];   // developer timing: cycles of thread 0 per phase, summed over CTAs
+#define GP_T(i) do { if (threadIdx.x == 0) { long long t1_ = clock64(); atomicAdd(&gp_dbg[i], (unsigned long long)(t1_ - t0_)); t0_ = t1_; } } while (0)
+#else
+#define GP_T(i)
+#endif
 
-__host__ __device__ inline size_t gp_smem_bytes(int d, int Nmax) {
+// Walkers per CTA is a template parameter: 32 (256 threads, two CTAs per SM: one CTA's K1 overlaps the other's K2 on the
+// shared FP64 pipe) or 64 (512 threads, one CTA per SM).  In-kernel clock64 timing on C3: K1 28.6 k + K2 23.6 k cycles
+// per 32-walker CTA with a co-resident CTA, K1 18.8 k + K2 39.0 k per 64-walker CTA alone; 32 x 2 wins (0.124 vs 0.138 ms).
+constexpr int GP_WT_MAX = 64;
+
+__host__ __device__ inline size_t gp_smem_bytes(int d, int Nmax, int GP_WT) {
     const int nks = ((Nmax + 15) / 16) * 4;   // K steps, padded to whole groups of 4
     size_t b = 0;
     b += sizeof(double) * (size_t)GP_WT * 4 * nks;   // sA  (32 walkers x 4*nks), operand-fragment-major
@@ -46,24 +56,120 @@ __host__ __device__ inline size_t gp_smem_bytes(int d, int Nmax) {
     return b;
 }
 
-__device__ __forceinline__ double stationary_kernel(int kind, double sq) {
-    // sq = squared scaled distance
-    if (kind == 3) return exp(-0.5 * sq);
-    const double r = sqrt(sq);
-    if (kind == 0) return exp(-r);
-    if (kind == 1) {
-        const double tt = r * 1.7320508075688772;     // math.sqrt(3) * dists
-        return (1.0 + tt) * exp(-tt);
-    }
-    const double tt = r * 2.23606797749979;            // math.sqrt(5) * dists
-    return (1.0 + tt + tt * tt / 3.0) * exp(-tt);
+// ---- K1 arithmetic ------------------------------------------------------------------------------------------------
+// The CUDA math library's sqrt() / exp() cost ~150 issued instructions per kernel value here (slow-path branches,
+// BSSY/BSYNC pairs and two UMOVs per polynomial coefficient); K1 is issue bound, so both are restated branch-free
+// for the only argument range that occurs (sq >= 0 finite, exp of a non-positive number), with every constant an
+// operand from constant memory.  Accuracy: sqrt is correctly rounded up to the last Newton correction (<= 1 ulp),
+// exp(-x) <= 2 ulp for x <= 700 (degree-13 Taylor on |r| <= ln2/2: remainder 4e-18) -- far inside the 1e-13
+// relative tolerance of the kernel-vector parity test, and both agree with libm on the test fixtures to <= 4e-16.
+__constant__ double GP_EXP_C[16] = {
+    1.4426950408889634074,       // 0  log2(e)
+    6.93147180369123816490e-01,  // 1  ln2_hi
+    1.90821492927058770002e-10,  // 2  ln2_lo
+    6755399441055744.0,          // 3  1.5 * 2^52: adding it rounds to nearest integer and leaves it in the low word
+    1.0 / 6227020800.0,          // 4  1/13!
+    1.0 / 479001600.0,           // 5  1/12!
+    1.0 / 39916800.0,            // 6  1/11!
+    1.0 / 3628800.0,             // 7  1/10!
+    1.0 / 362880.0,              // 8  1/9!
+    1.0 / 40320.0,               // 9  1/8!
+    1.0 / 5040.0,                // 10 1/7!
+    1.0 / 720.0,                 // 11 1/6!
+    1.0 / 120.0,                 // 12 1/5!
+    1.0 / 24.0,                  // 13 1/4!
+    1.0 / 6.0,                   // 14 1/3!
+    700.0                        // 15 clamp: exp(-700) = 1e-304 is still a normal number
+};
+
+__device__ __forceinline__ double exp_neg(double x) {   // exp(-x), x >= 0
+    x = fmin(x, GP_EXP_C[15]);
+    const double tm = fma(x, -GP_EXP_C[0], GP_EXP_C[3]);
+    const double nf = tm - GP_EXP_C[3];                 // n = rint(-x log2 e) <= 0
+    double r = fma(nf, -GP_EXP_C[1], -x);
+    r = fma(nf, -GP_EXP_C[2], r);                       // r = -x - n ln2, |r| <= ln2 / 2
+    double p = GP_EXP_C[4];
+#pragma unroll
+    for (int i = 5; i <= 14; ++i) p = fma(p, r, GP_EXP_C[i]);
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    const int n = __double2loint(tm);
+    return p * __hiloint2double((n + 1023) << 20, 0);   // n >= -1010: the scale is a normal power of two
 }
 
-// grid: (ceil(W / 32), n_pc_selected).  pcs[blockIdx.y + pc_first] describes the PC.
+__device__ __forceinline__ double sqrt_pos(double s) {  // sqrt(s), s >= 0 finite; returns 1e-150 for s < 1e-300
+    s = fmax(s, 1e-300);
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(s));   // MUFU.RSQ64H, ~2^-20 relative
+    double g = s * y, h = 0.5 * y;                      // coupled (Goldschmidt) iteration: g -> sqrt(s), h -> 1/(2 sqrt(s))
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+        const double r = fma(-g, h, 0.5);
+        g = fma(g, r, g);
+        h = fma(h, r, h);
+    }
+    return fma(fma(-g, g, s), h, g);                    // one Newton correction of the rounded result
+}
+
+template <int kind>
+__device__ __forceinline__ double stationary_kernel(double sq) {
+    // sq = squared scaled distance
+    if (kind == 3) return exp_neg(0.5 * sq);
+    const double r = sqrt_pos(sq);
+    if (kind == 0) return exp_neg(r);
+    if (kind == 1) {
+        const double tt = r * 1.7320508075688772;     // math.sqrt(3) * dists
+        const double e = exp_neg(tt);
+        return fma(tt, e, e);                          // (1 + tt) exp(-tt)
+    }
+    const double tt = r * 2.23606797749979;            // math.sqrt(5) * dists
+    return fma(tt * tt, 1.0 / 3.0, 1.0 + tt) * exp_neg(tt);
+}
+
+// K1 for one (walker tile, PC): thread = (walker tid/8, design points tid%8 + 8u + 32i), four design points at a time
+// so that four independent sqrt/exp dependency chains interleave.
+template <bool DO_GP, int KIND>
+__device__ __forceinline__ void gp_k1_loop(double* sA, const double* sX, const double* sTh, const PcDesc& pc, int d, int nks,
+                                           long long w0, long long W, double* __restrict__ k_out, int k_npc) {
+    const int tid = threadIdx.x, N = pc.N;
+    const int wl = tid >> 3, jl = tid & 7;
+    const double* th = sTh + wl * d;
+    double* krow = (k_out != nullptr && w0 + wl < W) ? k_out + ((w0 + wl) * k_npc + pc.local) * N : nullptr;
+    // of_index(wl, jl + 8u + 32i, nks) = base + 64 u + 256 i
+    double* sArow = sA + ((((wl >> 3) * nks + (jl >> 2)) << 5) + ((wl & 7) << 2) + (jl & 3));
+    const double cst = pc.cst;
+    for (int jb = jl; jb < N; jb += 32, sArow += 256) {
+        double sq[4] = {0.0, 0.0, 0.0, 0.0};
+        const double* xj[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) xj[u] = sX + min(jb + 8 * u, N - 1);
+        for (int k = 0; k < d; ++k) {
+            const double tk = th[k];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const double df = tk - xj[u][k * N];
+                sq[u] = fma(df, df, sq[u]);
+            }
+        }
+        double kv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) kv[u] = stationary_kernel<KIND>(sq[u]) + cst;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (jb + 8 * u < N) {
+                if (DO_GP) sArow[64 * u] = kv[u];
+                if (krow != nullptr) krow[jb + 8 * u] = kv[u];
+            }
+        }
+    }
+}
+
+// grid: (ceil(W / GP_WT), n_pc_selected).  pcs[blockIdx.y + pc_first] describes the PC.
 // k_out (optional): (W, k_ld_pc, N) row-major slice for this group, PC index = desc.local.
 // m_out / v_out (optional): (W, Ptot) at column blockIdx.y + pc_first.
-template <bool DO_GP>
-__global__ void __launch_bounds__(GP_THREADS, 2) gp_predict_kernel(const PcDesc* __restrict__ pcs, int pc_first, int d,
+template <bool DO_GP, int GP_WT>
+__global__ void __launch_bounds__(GP_WT * 8, GP_WT == 32 ? 2 : 1) gp_predict_kernel(const PcDesc* __restrict__ pcs, int pc_first, int d,
                                                                 const double* __restrict__ theta, long long W,
                                                                 double* __restrict__ k_out, int k_npc,
                                                                 double* __restrict__ m_out, double* __restrict__ v_out,
@@ -77,8 +183,13 @@ __global__ void __launch_bounds__(GP_THREADS, 2) gp_predict_kernel(const PcDesc*
     double* sSq = sTh + GP_WT * d;
     double* sMn = sSq + GP_WT * 4;
 
+    constexpr int GP_THREADS = GP_WT * 8;
+    constexpr int WM = GP_WT / 16;          // warps along the walker rows
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long w0 = (long long)blockIdx.x * GP_WT;
+#ifdef GP_TIMING
+    long long t0_ = clock64();
+#endif
 
     for (int idx = tid; idx < d * N; idx += GP_THREADS) sX[idx] = __ldg(pc.XsT + idx);
     for (int idx = tid; idx < GP_WT * d; idx += GP_THREADS) {
@@ -95,93 +206,134 @@ __global__ void __launch_bounds__(GP_THREADS, 2) gp_predict_kernel(const PcDesc*
         }
     }
     __syncthreads();
+    GP_T(0);
 
     // ---- K1 -------------------------------------------------------------------------------------------------
-    for (int idx = tid; idx < GP_WT * N; idx += GP_THREADS) {
-        const int wl = idx / N, j = idx - wl * N;
-        double sq = 0.0;
-        for (int k = 0; k < d; ++k) {
-            const double df = sTh[wl * d + k] - sX[k * N + j];
-            sq = fma(df, df, sq);
-        }
-        const double kv = stationary_kernel(pc.kind, sq) + pc.cst;
-        if (DO_GP) sA[of_index(wl, j, nks)] = kv;
-        if (k_out != nullptr && w0 + wl < W) k_out[((w0 + wl) * k_npc + pc.local) * N + j] = kv;
+    switch (pc.kind) {   // the kernel kind is a template parameter of the loop so that its four chains interleave
+        case 0: gp_k1_loop<DO_GP, 0>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc); break;
+        case 1: gp_k1_loop<DO_GP, 1>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc); break;
+        case 2: gp_k1_loop<DO_GP, 2>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc); break;
+        default: gp_k1_loop<DO_GP, 3>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc); break;
     }
     if (!DO_GP) return;
+    GP_T(1);
     __syncthreads();
+    GP_T(2);
 
     // ---- K2 -------------------------------------------------------------------------------------------------
-    // warp (wm, wn): walker rows wm*16.., n-tiles {t : snake(t) == wn}.  The B operand (rows of L^-1, L2 resident,
-    // shared by every CTA of this PC) is streamed global -> registers in groups of 4 k-steps, one group ahead of the
-    // DMMAs that consume it (the loads' L2 latency is what bounded the first version of this kernel).
-    const int wm = warp & 1;    // rows wm*16 .. wm*16+15
-    const int wn = warp >> 1;   // n-tile owner 0..3
+    // warp (wm, wn): walker rows wm*16.., fragment groups {q : snake(q) == wn}.  The B operand is cut into n-fragments
+    // of 8 rows of L^-1 (fragment f = rows 8f .. 8f+7; row N holds alpha).  Fragment f only needs the k-steps
+    // 0 .. min(ceil(N/4), 2f+2) - 1 (L^-1 is lower triangular) and fragments past row N do not exist, so the fragments
+    // are grouped four at a time from the TOP (group 0 = the four longest) and the groups dealt to the four n-owners
+    // in snake order: every owner gets the same number of DMMAs to within a few per cent (C3: 216..222 fragment
+    // k-steps of 870).  B (L2 resident, shared by every CTA of this PC) is streamed global -> registers in groups
+    // of 4 k-steps, one group ahead of the DMMAs that consume it.
+    const int wm = warp % WM;   // rows wm*16 .. wm*16+15
+    const int wn = warp / WM;   // fragment-group owner 0..3
     const int g = lane >> 2, t = lane & 3;
     double sumsq[2] = {0.0, 0.0};
     double meanv[2] = {0.0, 0.0};
     const double* sAw = sA + (size_t)(2 * wm) * nks * 32 + lane;
-    const size_t tile_stride = (size_t)4 * nks * 32;
+    const double* Bl = pc.LinvF + lane;
+    const int kfull = (N + 3) >> 2;
+    const int ftop = N >> 3;                        // fragment holding row N
+    const int ngroups = (ftop + 4) >> 2;
 
-    auto tile_of = [&](int idx) {   // idx-th n-tile owned by this warp (snake order balances the triangle)
+    auto group_of = [&](int idx) {   // idx-th fragment group owned by this warp
         const int blk = idx >> 1;
         return blk * 8 + ((idx & 1) ? 7 - wn : wn);
     };
-    auto load_group = [&](double (&bb)[4][4], int tile, int grp) {
-        const double* Bt = pc.LinvF + (size_t)tile * tile_stride + (size_t)(grp * 4) * 32 + lane;
+    auto klim_of = [&](int f) { return f < 0 ? 0 : min(kfull, 2 * f + 2); };
+    // loads are never predicated: past a fragment's triangle the packed operand holds zeros (4*grp+3 < nks always),
+    // and the fragments a bottom group lacks are clamped to fragment 0 and never multiplied
+    auto load_group = [&](double (&bb)[4][4], int f0, int grp) {
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
+        for (int nf = 0; nf < 4; ++nf) {
+            const double* bp = Bl + ((size_t)max(f0 - nf, 0) * nks + 4 * grp) * 32;
 #pragma unroll
-            for (int nf = 0; nf < 4; ++nf) bb[kk][nf] = __ldg(Bt + ((size_t)nf * nks + kk) * 32);
+            for (int kk = 0; kk < 4; ++kk) bb[kk][nf] = __ldg(bp + kk * 32);
+        }
     };
 
     int idx = 0;
-    int tile = tile_of(0);
-    if (tile < pc.ntn) {
+    int q = group_of(0);
+    if (q < ngroups) {
         double bcur[4][4], bnxt[4][4];
-        load_group(bcur, tile, 0);
-        while (tile < pc.ntn) {
-            const int ngrp = min(nks, 8 * (tile + 1)) >> 2;   // nks is a multiple of 4
+        load_group(bcur, ftop - 4 * q, 0);
+        while (q < ngroups) {
+            const int f0 = ftop - 4 * q;
+#ifdef GP_EXP_NOK2
+            const int ngrp = 1;
+#else
+            const int ngrp = (klim_of(f0) + 3) >> 2;
+#endif
+            const int kl3 = klim_of(f0 - 3);       // the shortest fragment of the group
             double acc[2][4][2];
 #pragma unroll
             for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
                 for (int nf = 0; nf < 4; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
-            const int next_tile = tile_of(idx + 1);
+            const int next_q = group_of(idx + 1);
             for (int grp = 0; grp < ngrp; ++grp) {
-                // prefetch the next group (of this tile, or the first of the next tile)
-                if (grp + 1 < ngrp) load_group(bnxt, tile, grp + 1);
-                else if (next_tile < pc.ntn) load_group(bnxt, next_tile, 0);
+                // prefetch the next group of k-steps (of this fragment group, or the first of the next one)
+                if (grp + 1 < ngrp) load_group(bnxt, f0, grp + 1);
+                else if (next_q < ngroups) load_group(bnxt, ftop - 4 * next_q, 0);
+                if (4 * grp + 4 <= kl3) {
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk) {
-                    double a[2];
+                    for (int kk = 0; kk < 4; ++kk) {
+                        double a[2];
 #pragma unroll
-                    for (int mi = 0; mi < 2; ++mi) a[mi] = sAw[(mi * nks + grp * 4 + kk) * 32];
+                        for (int mi = 0; mi < 2; ++mi) a[mi] = sAw[(mi * nks + grp * 4 + kk) * 32];
 #pragma unroll
-                    for (int mi = 0; mi < 2; ++mi)
+                        for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
-                        for (int nf = 0; nf < 4; ++nf) dmma(acc[mi][nf], a[mi], bcur[kk][nf]);
+                            for (int nf = 0; nf < 4; ++nf) dmma(acc[mi][nf], a[mi], bcur[kk][nf]);
+                    }
+                } else {
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        const int ks = grp * 4 + kk;
+                        double a[2];
+#pragma unroll
+                        for (int mi = 0; mi < 2; ++mi) a[mi] = sAw[(mi * nks + ks) * 32];
+#pragma unroll
+                        for (int nf = 0; nf < 4; ++nf)
+                            if (ks < klim_of(f0 - nf)) {
+#pragma unroll
+                                for (int mi = 0; mi < 2; ++mi) dmma(acc[mi][nf], a[mi], bcur[kk][nf]);
+                            }
+                    }
                 }
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk)
 #pragma unroll
                     for (int nf = 0; nf < 4; ++nf) bcur[kk][nf] = bnxt[kk][nf];
             }
+            if (f0 == ftop) {
+                // the top fragment holds row N (= alpha: the mean) and nothing past it counts
 #pragma unroll
-            for (int mi = 0; mi < 2; ++mi)
+                for (int e = 0; e < 2; ++e) {
+                    const int n = f0 * 8 + 2 * t + e;
 #pragma unroll
-                for (int nf = 0; nf < 4; ++nf)
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const int n = tile * 32 + nf * 8 + 2 * t + e;
-                        const double x = acc[mi][nf][e];
+                    for (int mi = 0; mi < 2; ++mi) {
+                        const double x = acc[mi][0][e];
                         if (n < N) sumsq[mi] = fma(x, x, sumsq[mi]);
                         else if (n == N) meanv[mi] = x;
                     }
+                }
+            }
+#pragma unroll
+            for (int nf = 0; nf < 4; ++nf) {
+                if (f0 - nf < 0 || (nf == 0 && f0 == ftop)) continue;
+#pragma unroll
+                for (int mi = 0; mi < 2; ++mi)
+                    sumsq[mi] = fma(acc[mi][nf][0], acc[mi][nf][0], fma(acc[mi][nf][1], acc[mi][nf][1], sumsq[mi]));
+            }
             ++idx;
-            tile = next_tile;
+            q = next_q;
         }
     }
+    GP_T(3);
 #pragma unroll
     for (int mi = 0; mi < 2; ++mi) {
         sumsq[mi] += __shfl_xor_sync(0xffffffffu, sumsq[mi], 1);
@@ -195,6 +347,7 @@ __global__ void __launch_bounds__(GP_THREADS, 2) gp_predict_kernel(const PcDesc*
         }
     }
     __syncthreads();
+    GP_T(4);
     if (tid < GP_WT) {
         const long long w = w0 + tid;
         if (w < W) {
