@@ -15,6 +15,7 @@
 #include "chol_pipe.cuh"
 #include "common.cuh"
 #include "cov_assemble.cuh"
+#include "ensemble.cuh"
 #include "gp_predict.cuh"
 #include "setup_kernels.cuh"
 #include "woodbury.cuh"
@@ -222,6 +223,12 @@ int launch_chol(bi_handle h, const double* dTheta, const double* dM, const doubl
                     double v = 0;
                     for (int wq = 0; wq < 8; ++wq) v += (double)hb[wq * 8 + c];
                     std::fprintf(stderr, "%s %.1f%%  ", nm[c], 100.0 * v / tot);
+                }
+                std::fprintf(stderr, "| wait_full by warp:");
+                for (int wq = 0; wq < 8; ++wq) {
+                    double tw = 0;
+                    for (int c = 0; c < 6; ++c) tw += (double)hb[wq * 8 + c];
+                    std::fprintf(stderr, " %.0f", 100.0 * hb[wq * 8 + 0] / tw);
                 }
                 std::fprintf(stderr, " | cycles/walker/warp %.0f | factor warp: potrf %.0f cyc/panel, idle %.0f cyc/panel\n", tot / 8.0 / (double)W,
                              (double)hb[6] / (double)W / h->nt, (double)hb[7] / (double)W / h->nt);
@@ -600,6 +607,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
                 return bail(BI_E_UNSUPPORTED);
             }
         }
+        if (const char* e = std::getenv("BI_CHOL_OCC")) occ = std::max(1, std::min(occ, std::atoi(e)));   // developer A/B knob
         h->chol_ctas = h->sm_count * occ;
         h->ws_stride = chol_ws_doubles(nt);
         TRY(dalloc(h, &h->dWs, (size_t)h->chol_ctas * h->ws_stride));
@@ -998,6 +1006,33 @@ int bi_loglikelihood_host(bi_handle h, const double* dy, const double* cov, int6
     if (e != cudaSuccess) { h->err = std::string("bi_loglikelihood_host: ") + cudaGetErrorString(e); rc = (int)e; }
     cudaFree(dCov); cudaFree(dDy); cudaFree(dWs); cudaFree(dLp); cudaFree(dInfo); cudaFree(dK);
     return rc;
+}
+
+// ---- stretch-move half-step around the log-posterior ---------------------------------------------------
+int bi_stretch_propose(bi_handle h, const double* coords, const int32_t* s_idx, const int32_t* c_idx, const double* zz,
+                       int64_t ns, double* q_out, void* stream) {
+    if (!h || !coords || !s_idx || !c_idx || !zz || !q_out || ns < 0) return fail(h, BI_E_ARG, "bad argument");
+    if (ns == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    const long long n = (long long)ns * h->d;
+    stretch_propose_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(coords, s_idx, c_idx, zz, ns, h->d, q_out);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int bi_stretch_accept(bi_handle h, double* coords, double* logp, const int32_t* s_idx, const double* q, const double* new_lp,
+                      const double* factors, const double* logu, int64_t ns, int64_t* n_accepted, int32_t* nan_flag,
+                      void* stream) {
+    if (!h || !coords || !logp || !s_idx || !q || !new_lp || !factors || !logu || !n_accepted || !nan_flag || ns < 0)
+        return fail(h, BI_E_ARG, "bad argument");
+    if (ns == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    stretch_accept_kernel<<<(unsigned)((ns + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        coords, logp, s_idx, q, new_lp, factors, logu, ns, h->d, reinterpret_cast<long long*>(n_accepted), nan_flag);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
 }
 
 }  // extern "C"

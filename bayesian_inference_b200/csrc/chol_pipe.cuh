@@ -33,7 +33,10 @@ namespace bi {
 #endif
 constexpr int PIPE_CONSUMERS = 8;
 constexpr int PIPE_THREADS = (PIPE_CONSUMERS + 2) * 32;   // + producer + factor warp
-constexpr int PIPE_STAGES = 4;
+#ifndef PIPE_NSTAGES
+#define PIPE_NSTAGES 4   // measured: 3, 4, 6 and 8 stages all leave the consumers' wait at 25-30 % -- the ring is not latency bound
+#endif
+constexpr int PIPE_STAGES = PIPE_NSTAGES;
 constexpr int STRIP_ELEMS = TILE_ELEMS / 2;                // 16 x 32 doubles = 4 KB
 constexpr int SUB_ELEMS = STRIP_ELEMS / 2;                 // 16 x 16 doubles = 2 KB: one K half of a strip
 constexpr int STAGE_ELEMS = 2 * SUB_ELEMS + PIPE_CONSUMERS * SUB_ELEMS;   // B piece (2 strips) + 8 A pieces = 20 KB
@@ -52,7 +55,7 @@ __host__ __device__ inline size_t pipe_smem_bytes(int Fp, int K0p) {
     b += sizeof(double) * (size_t)Fp;          // sDy
     b += sizeof(double) * (size_t)K0p * 2;     // sNegV, sM
     b += sizeof(double) * 16;                  // sRed (8) + logdet + spare
-    b += sizeof(unsigned long long) * 16;      // mbarriers
+    b += sizeof(unsigned long long) * 24;      // mbarriers
     b += sizeof(int) * (size_t)Fp;             // sObs
     b += sizeof(int) * 8;                      // flags
     b += sizeof(int) * 4 * (size_t)(Fp / 32);  // kmin, imax, tile_omin, tile_omax
@@ -297,7 +300,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
     double* sM = sNegV + K0p;
     double* sRed = sM + K0p;
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(sRed + 16);
-    int* sObs = reinterpret_cast<int*>(bars + 16);
+    int* sObs = reinterpret_cast<int*>(bars + 24);
     int* sFlag = sObs + P.Fp;
     int* sKmin = sFlag + 8;
     int* sImax = sKmin + P.nt;

@@ -221,6 +221,29 @@ class DeviceEmulator:
         return m, v
 
 
+    # ---- stretch-move half-step on device-resident state ------------------------------------------
+    def stretch_propose(self, coords, s_idx, c_idx, zz, q_out) -> None:
+        """q_out[k] = c - (c - s) * zz[k]; all arguments CUDA tensors (coords f64 (W,d), indices int32 (ns), zz f64 (ns))."""
+        import torch
+
+        stream = torch.cuda.current_stream(coords.device).cuda_stream
+        self._check(self._lib.bi_stretch_propose(self._h, C.c_void_p(coords.data_ptr()), C.c_void_p(s_idx.data_ptr()),
+                                                 C.c_void_p(c_idx.data_ptr()), C.c_void_p(zz.data_ptr()), int(s_idx.shape[0]),
+                                                 C.c_void_p(q_out.data_ptr()), C.c_void_p(stream)), "bi_stretch_propose")
+
+    def stretch_accept(self, coords, logp, s_idx, q, new_lp, factors, logu, n_accepted, nan_flag) -> None:
+        """Accept/reject one half-step in place (coords, logp, n_accepted int64 (W), nan_flag int32 (1))."""
+        import torch
+
+        stream = torch.cuda.current_stream(coords.device).cuda_stream
+        self._check(self._lib.bi_stretch_accept(self._h, C.c_void_p(coords.data_ptr()), C.c_void_p(logp.data_ptr()),
+                                                C.c_void_p(s_idx.data_ptr()), C.c_void_p(q.data_ptr()),
+                                                C.c_void_p(new_lp.data_ptr()), C.c_void_p(factors.data_ptr()),
+                                                C.c_void_p(logu.data_ptr()), int(s_idx.shape[0]),
+                                                C.c_void_p(n_accepted.data_ptr()), C.c_void_p(nan_flag.data_ptr()),
+                                                C.c_void_p(stream)), "bi_stretch_accept")
+
+
 def from_analysis(emulation_config, emulation_results, *, min, max, experimental_results=None, sigma_exp=None,
                   device: int = 0, max_batch: int = 0) -> DeviceEmulator:
     """Pack what ``mcmc.run_mcmc`` loads (mcmc.py:48-67) and upload it."""

@@ -148,6 +148,132 @@ class StretchEnsemble:
         return result
 
 
+def draw_stretch_randoms(rng: np.random.RandomState, nwalkers: int, ndim: int, nsteps: int, a: float = 2.0) -> dict:
+    """Everything ``nsteps`` stretch-move steps draw from ``rng``, in emcee's consumption order.
+
+    None of it depends on the chain state: per step one uniform (move selection), the shuffled red/blue split, and per
+    half ``rand(ns)`` (stretch factors), ``randint(nc, size=ns)`` (partners) and ``rand(ns)`` (acceptance).  Returned
+    arrays have shape (nsteps, 2, W/2): ``s_idx`` the walkers moved, ``c_idx`` their partners (walker ids), ``zz``,
+    ``factors = (ndim-1) log zz`` and ``logu = log(u)`` -- the logs are taken here, on the host, so that the device
+    accept test compares exactly the numbers the host sampler compares.
+    """
+    W, ns = nwalkers, nwalkers // 2
+    out = {"s_idx": np.empty((nsteps, 2, ns), np.int32), "c_idx": np.empty((nsteps, 2, ns), np.int32),
+           "zz": np.empty((nsteps, 2, ns)), "factors": np.empty((nsteps, 2, ns)), "logu": np.empty((nsteps, 2, ns))}
+    all_inds = np.arange(W)
+    for t in range(nsteps):
+        rng.random_sample()
+        inds = all_inds % 2
+        rng.shuffle(inds)
+        for split in range(2):
+            S1 = inds == split
+            s_ids, c_ids = all_inds[S1], all_inds[~S1]
+            zz = ((a - 1.0) * rng.rand(ns) + 1.0) ** 2.0 / a
+            rint = rng.randint(c_ids.shape[0], size=(ns,))
+            with np.errstate(divide="ignore"):
+                logu = np.log(rng.rand(ns))
+            out["s_idx"][t, split], out["c_idx"][t, split] = s_ids, c_ids[rint]
+            out["zz"][t, split], out["factors"][t, split], out["logu"][t, split] = zz, (ndim - 1.0) * np.log(zz), logu
+    return out
+
+
+class DeviceStretchEnsemble(StretchEnsemble):
+    """The same sampler with the chain state resident on the GPU.
+
+    Per half-step: ``bi_stretch_propose`` -> ``bi_log_posterior`` (K1+K2, K4) -> [all-gather of log-probabilities when
+    sharded over ranks] -> ``bi_stretch_accept``, all enqueued on torch's current stream; the host only generates the
+    chain-independent random numbers (``draw_stretch_randoms``) one block of steps ahead and reads the chain back one
+    block at a time.  Same RandomState consumption and the same rounded arithmetic as ``StretchEnsemble``, hence the
+    same chain (tests/test_gpu_chain.py).  A NaN log-probability raises ``ValueError`` like emcee, at the end of the
+    block it occurred in.
+    """
+
+    def __init__(self, nwalkers: int, ndim: int, device_emulator, mode: str = "dense", a: float = 2.0,
+                 seed: Optional[int] = None, random_state: Optional[np.random.RandomState] = None, block: int = 64,
+                 group=None):
+        self.dev, self.mode, self.block, self.group = device_emulator, mode, int(block), group
+        super().__init__(nwalkers, ndim, log_prob_fn=None, a=a, seed=seed, random_state=random_state)
+        if ndim != device_emulator.d:
+            raise ValueError(f"ndim {ndim} does not match the emulator's parameter dimension {device_emulator.d}")
+        self.world, self.rank = 1, 0
+        try:
+            import torch.distributed as dist
+
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+                self.world, self.rank, self._dist = dist.get_world_size(group), dist.get_rank(group), dist
+        except Exception:
+            pass
+
+    def _device_log_prob(self, q, out):
+        """out[:n] = log posterior of the n rows of q (CUDA tensors), sharded over ranks when distributed."""
+        n = q.shape[0]
+        if self.world == 1:
+            self.dev.log_posterior_tensor(q, n_div=1.0, mode=self.mode, out=out[:n])
+        else:
+            lo, hi = ShardedLogProb.bounds(n, self.world, self.rank)
+            per = (n + self.world - 1) // self.world
+            if hi > lo:
+                self.dev.log_posterior_tensor(q[lo:hi], n_div=1.0, mode=self.mode, out=self._send[:hi - lo])
+            self._dist.all_gather_into_tensor(self._recv[:per * self.world], self._send[:per], group=self.group)
+            out[:n].copy_(self._recv[:n])
+        self.n_log_prob_calls += 1
+        self.n_log_prob_rows += n
+
+    def sample(self, initial_state: np.ndarray, iterations: int = 1, log_prob0: Optional[np.ndarray] = None):
+        import torch
+
+        x0 = np.array(initial_state, dtype=np.float64, copy=True)
+        W, nd, ns = self.nwalkers, self.ndim, self.nwalkers // 2
+        if x0.shape != (W, nd):
+            raise ValueError("incompatible input dimensions")
+        if np.linalg.cond(np.cov(x0, rowvar=False).reshape(nd, nd)) > 1e8:
+            raise ValueError("Initial state has a large condition number. Make sure that your walkers are linearly independent.")
+        device = torch.device("cuda", self.dev.device)
+        with torch.cuda.device(device):
+            coords = torch.from_numpy(x0).to(device)
+            logp = torch.empty(W, dtype=torch.float64, device=device)
+            per = (W + self.world - 1) // self.world
+            self._send = torch.full((per,), float("nan"), dtype=torch.float64, device=device)
+            self._recv = torch.empty(per * self.world, dtype=torch.float64, device=device)
+            if log_prob0 is None:
+                self._device_log_prob(coords, logp)
+            else:
+                logp.copy_(torch.from_numpy(np.array(log_prob0, dtype=np.float64)))
+            if bool(torch.isnan(logp).any()):
+                raise ValueError("Probability function returned NaN")
+            q = torch.empty((ns, nd), dtype=torch.float64, device=device)
+            new_lp = torch.empty(ns, dtype=torch.float64, device=device)
+            n_acc = torch.zeros(W, dtype=torch.int64, device=device)
+            nan_flag = torch.zeros(1, dtype=torch.int32, device=device)
+            done = 0
+            while done < iterations:
+                nb = min(self.block, iterations - done)
+                r = draw_stretch_randoms(self._random, W, nd, nb, self.a)
+                rd = {k: torch.from_numpy(v).pin_memory().to(device, non_blocking=True) for k, v in r.items()}
+                chain_b = torch.empty((nb, W, nd), dtype=torch.float64, device=device)
+                lp_b = torch.empty((nb, W), dtype=torch.float64, device=device)
+                for t in range(nb):
+                    for split in range(2):
+                        s_idx = rd["s_idx"][t, split]
+                        self.dev.stretch_propose(coords, s_idx, rd["c_idx"][t, split], rd["zz"][t, split], q)
+                        self._device_log_prob(q, new_lp)
+                        self.dev.stretch_accept(coords, logp, s_idx, q, new_lp, rd["factors"][t, split], rd["logu"][t, split],
+                                                n_acc, nan_flag)
+                    chain_b[t].copy_(coords)
+                    lp_b[t].copy_(logp)
+                chain_h, lp_h = chain_b.cpu().numpy(), lp_b.cpu().numpy()      # synchronises: the block is done
+                if int(nan_flag.item()):
+                    raise ValueError("Probability function returned NaN")
+                self._accepted += n_acc.cpu().numpy()
+                n_acc.zero_()
+                for t in range(nb):
+                    self.iteration += 1
+                    self._chain.append(chain_h[t])
+                    self._log_prob.append(lp_h[t])
+                    yield chain_h[t], lp_h[t]
+                done += nb
+
+
 class ShardedLogProb:
     """Walker sharding over ranks: each rank evaluates a contiguous slice of the rows, one all-gather of
     the log-probabilities closes the call.  Every rank runs the identical sampler (same seed), so proposals and

@@ -6,9 +6,10 @@ Same sequence as the reference: random start in the prior box -> first half of b
 experimental_pseudodata]`` (mcmc.py:111-125).
 
 Differences, all forced by what is (not) installed here or by the move to the GPU:
-* no ``multiprocessing`` pool: ``initialize_pool_variables`` loads the emulators into HBM once and the sampler calls
-  ``log_posterior_walkers`` once per half-step for all proposals (``StretchEnsemble``, a restatement of emcee's stretch
-  move; emcee itself is not installed in this image);
+* no ``multiprocessing`` pool: ``initialize_pool_variables`` loads the emulators into HBM once and the sampler
+  evaluates all proposals of a half-step in one call (``StretchEnsemble`` / ``DeviceStretchEnsemble``, restatements
+  of emcee's stretch move; emcee itself is not installed in this image); by default the ensemble itself lives on the
+  GPU and only the chain-independent random numbers come from the host;
 * with ``torch.distributed`` initialised (one process per GPU) the proposals are sharded over the ranks and one
   all-gather of log-probabilities closes each half-step;
 * ``seed`` makes the run reproducible (the reference never seeds, mcmc.py:88);
@@ -26,7 +27,7 @@ from typing import Any, Optional
 import numpy as np
 
 from . import log_posterior
-from .ensemble import ShardedLogProb, StretchEnsemble
+from .ensemble import DeviceStretchEnsemble, ShardedLogProb, StretchEnsemble
 
 logger = logging.getLogger(__name__)
 
@@ -54,8 +55,12 @@ def _write_results(output_dict: dict[str, Any], config) -> str:
 
 def run_mcmc(config, closure_index: int = -1, *, emulation_config=None, emulation_results=None,
              experimental_results=None, design_point=None, seed: Optional[int] = None, mode: str = "dense",
-             sigma_exp: Optional[np.ndarray] = None, write: bool = True) -> dict[str, Any]:
-    """Run burn-in + production and return (and write) the reference's output dictionary."""
+             sigma_exp: Optional[np.ndarray] = None, write: bool = True, sampler: str = "device") -> dict[str, Any]:
+    """Run burn-in + production and return (and write) the reference's output dictionary.
+
+    ``sampler='device'`` keeps the ensemble on the GPU (``DeviceStretchEnsemble``: propose / accept kernels around the
+    log-posterior kernels, no host round trip per half-step); ``sampler='host'`` runs the numpy stretch move and calls
+    the log-posterior once per half-step.  Both consume the random stream identically and produce the same chain."""
     par = config.analysis_config["parameterization"][config.parameterization]
     names, lo, hi = par["names"], np.asarray(par["min"], dtype=np.float64), np.asarray(par["max"], dtype=np.float64)
     ndim = len(names)
@@ -81,11 +86,16 @@ def run_mcmc(config, closure_index: int = -1, *, emulation_config=None, emulatio
 
     log_posterior.initialize_pool_variables(lo, hi, emulation_config, emulation_results, experimental_results, None,
                                             sigma_exp=sigma_exp, mode=mode)
-    fn = log_posterior.log_posterior_walkers
-    if distributed:
-        fn = ShardedLogProb(fn)
     rng = np.random.RandomState(seed)
-    sampler = StretchEnsemble(config.n_walkers, ndim, fn, random_state=rng)
+    if sampler == "device":
+        sampler = DeviceStretchEnsemble(config.n_walkers, ndim, log_posterior.device(), mode=mode, random_state=rng)
+    elif sampler == "host":
+        fn = log_posterior.log_posterior_walkers
+        if distributed:
+            fn = ShardedLogProb(fn)
+        sampler = StretchEnsemble(config.n_walkers, ndim, fn, random_state=rng)
+    else:
+        raise ValueError("sampler must be 'device' or 'host'")
 
     logger.info("Initializing sampler...")
     random_pos = rng.uniform(lo, hi, (config.n_walkers, ndim))                       # mcmc.py:88

@@ -13,6 +13,7 @@
  *   emulation.predict (merged)               emulation.py:410-462  bi_predict[_host]
  *   log_posterior.log_posterior              log_posterior.py:42   bi_log_posterior[_host]
  *   log_posterior._loglikelihood             log_posterior.py:104  bi_loglikelihood_host
+ *   emcee stretch move driven by mcmc.run_mcmc  mcmc.py:83-107     bi_stretch_propose / bi_stretch_accept
  *
  * Conventions
  *   - every matrix is row-major float64; every index is 0-based;
@@ -148,6 +149,22 @@ int bi_log_posterior_host(bi_handle h, const double* theta, int64_t W, double n_
  * log_posterior.py:104-146.  F' is arbitrary (need not equal the handle's F). */
 int bi_loglikelihood_host(bi_handle h, const double* dy, const double* cov, int64_t n, int32_t Fdim,
                           double* out, int32_t* info_out);
+
+/* ---- the sampler step around the log-posterior (mcmc.py:83-107 -> emcee 3.1.4 RedBlueMove.propose / StretchMove) ----
+ * One half-step of the stretch move on device-resident state; everything drawn from the random stream (split, zz,
+ * partners, acceptance uniforms) is chain-independent and is generated by the host in emcee's order.
+ * All pointers are DEVICE pointers; both calls enqueue on `stream` and return without synchronising.
+ *
+ * bi_stretch_propose: q_out[k][:] = c - (c - s) * zz[k] with s = coords[s_idx[k]], c = coords[c_idx[k]]; q_out (ns, d).
+ * bi_stretch_accept : for each k, if (factors[k] + new_lp[k]) - logp[s_idx[k]] > logu[k]: coords[s_idx[k]] = q[k],
+ *                     logp[s_idx[k]] = new_lp[k], n_accepted[s_idx[k]] += 1.  A NaN in new_lp sets *nan_flag = 1 and
+ *                     accepts nothing for that row (emcee raises ValueError; the host mirror does so when it reads
+ *                     the flag).  s_idx must not contain duplicates (one half of the ensemble). */
+int bi_stretch_propose(bi_handle h, const double* coords, const int32_t* s_idx, const int32_t* c_idx, const double* zz,
+                       int64_t ns, double* q_out, void* stream);
+int bi_stretch_accept(bi_handle h, double* coords, double* logp, const int32_t* s_idx, const double* q,
+                      const double* new_lp, const double* factors, const double* logu, int64_t ns,
+                      int64_t* n_accepted, int32_t* nan_flag, void* stream);
 
 #ifdef __cplusplus
 }

@@ -88,11 +88,11 @@ def test_run_mcmc_driver_sequence(monkeypatch, tmp_path):
         analysis_config={"parameterization": {"p": {"names": ["a", "b", "c"], "min": list(z["min"]), "max": list(z["max"])}}},
         parameterization="p", analysis_name="toy", config_file="", output_dir=str(tmp_path), mcmc_output_dir=str(tmp_path),
         n_walkers=8, n_burn_steps=6, n_sampling_steps=5, n_logging_steps=2, sampler_outputfile=str(tmp_path / "s.pkl"))
-    out = mcmc.run_mcmc(cfg, emulation_config=object(), emulation_results={}, experimental_results={}, seed=5)
+    out = mcmc.run_mcmc(cfg, emulation_config=object(), emulation_results={}, experimental_results={}, seed=5, sampler="host")
     assert out["chain"].shape == (5, 8, 3) and out["log_prob"].shape == (5, 8) and out["acceptance_fraction"].shape == (8,)
     assert out["autocorrelation_time"] is None            # chain far too short: recorded as None, like the reference
     assert out["n_log_prob_rows"] == (8 + 3 * 8) + (8 + 3 * 8) + (8 + 5 * 8)   # two burn-in halves + production, W rows per step
-    again = mcmc.run_mcmc(cfg, emulation_config=object(), emulation_results={}, experimental_results={}, seed=5, write=False)
+    again = mcmc.run_mcmc(cfg, emulation_config=object(), emulation_results={}, experimental_results={}, seed=5, write=False, sampler="host")
     assert np.array_equal(out["chain"], again["chain"])
     assert (tmp_path / "mcmc.npz").exists() or (tmp_path / "mcmc.h5").exists()
 
@@ -145,3 +145,32 @@ def test_sharded_logprob_gloo_world2():
         assert first_rows == (4 if rank == 0 else 3)                 # each rank evaluated only its slice
     assert ShardedLogProb.bounds(7, 2, 0) == (0, 4) and ShardedLogProb.bounds(7, 2, 1) == (4, 7)
     assert ShardedLogProb.bounds(2, 4, 3) == (2, 2)                  # more ranks than rows: empty slice
+
+
+def test_predrawn_randoms_reproduce_the_sampler_stream():
+    """draw_stretch_randoms consumes the RandomState exactly as StretchEnsemble.sample does: replaying its arrays with
+    numpy gives the identical chain (this is what the device-resident sampler uploads)."""
+    from bayesian_inference_b200.ensemble import StretchEnsemble, draw_stretch_randoms
+
+    W, nd, steps = 20, 3, 60
+    f = lambda X: -0.5 * np.sum(X ** 2, axis=1)
+    x0 = np.random.RandomState(7).normal(size=(W, nd))
+    s = StretchEnsemble(W, nd, f, random_state=np.random.RandomState(11))
+    s.run_mcmc(x0, steps)
+    rng = np.random.RandomState(11)
+    r = draw_stretch_randoms(rng, W, nd, 25)
+    r2 = draw_stretch_randoms(rng, W, nd, steps - 25)        # block boundaries do not disturb the stream
+    r = {k: np.concatenate([r[k], r2[k]]) for k in r}
+    coords, lp, chain = x0.copy(), f(x0), []
+    for t in range(steps):
+        for sp in range(2):
+            si, ci = r["s_idx"][t, sp], r["c_idx"][t, sp]
+            assert len(set(si)) == W // 2 and not set(si) & set(ci)
+            c, sx = coords[ci], coords[si]
+            q = c - (c - sx) * r["zz"][t, sp][:, None]
+            nl = f(q)
+            acc = (r["factors"][t, sp] + nl - lp[si]) > r["logu"][t, sp]
+            coords[si[acc]] = q[acc]
+            lp[si[acc]] = nl[acc]
+        chain.append(coords.copy())
+    assert np.array_equal(np.array(chain), s.get_chain())

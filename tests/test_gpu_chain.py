@@ -36,3 +36,48 @@ def test_chain_trace_identical_for_1000_steps(mode):
     fin = np.isfinite(cpu.get_log_prob())
     assert np.max(np.abs(gpu.get_log_prob()[fin] - cpu.get_log_prob()[fin]) / np.abs(cpu.get_log_prob()[fin])) < 1e-9
     assert 0.05 < gpu.acceptance_fraction.mean() < 0.95
+
+
+@pytest.mark.parametrize("mode", ["dense", "woodbury"])
+def test_device_resident_sampler_matches_host_sampler(mode):
+    """DeviceStretchEnsemble (propose / accept kernels, state in HBM) == StretchEnsemble driven by the same CUDA
+    log-posterior: identical chain, log-probabilities and acceptance counts for 1000 steps (bit for bit)."""
+    from bayesian_inference_b200.device import DeviceEmulator
+    from bayesian_inference_b200.ensemble import DeviceStretchEnsemble
+
+    z, _ = load_golden("mid")
+    W, nsteps, seed, d = 32, 1000, 77, int(z["d"])
+    x0 = np.random.RandomState(3).uniform(0.1, 0.9, (W, d))
+    x0[0, 0] = 1.5      # one walker starts outside the prior box: logp = -inf, it must move in or stay, never NaN
+    with DeviceEmulator(image.EmulatorImage.from_flat(z)) as dev:
+        host = StretchEnsemble(W, d, lambda X: dev.log_posterior(X, n_div=1.0, mode=mode), seed=seed)
+        host.run_mcmc(x0, nsteps)
+        devs = DeviceStretchEnsemble(W, d, dev, mode=mode, seed=seed, block=96)     # 1000 = 10 x 96 + 40: ragged last block
+        last = devs.run_mcmc(x0, nsteps)
+    assert np.array_equal(devs.get_chain(), host.get_chain())
+    assert np.array_equal(devs.get_log_prob(), host.get_log_prob())
+    assert np.array_equal(devs.acceptance_fraction, host.acceptance_fraction)
+    assert np.array_equal(last[0], host.get_chain()[-1])
+    assert devs.n_log_prob_rows == host.n_log_prob_rows
+
+
+def test_device_sampler_raises_on_nan_like_emcee():
+    """A covariance that is not positive definite gives NaN; emcee raises ValueError, so does the device sampler."""
+    from bayesian_inference_b200.device import DeviceEmulator
+    from bayesian_inference_b200.ensemble import DeviceStretchEnsemble
+
+    z, _ = load_golden("toy")
+    z = dict(z)
+    z["y_err"] = np.zeros_like(z["y_err"])
+    z["A"] = None if "A" not in z else z["A"]
+    img = image.EmulatorImage.from_flat(z)
+    img.y_err = np.zeros_like(img.y_err)
+    for g in img.groups:          # no truncated-PC covariance either: C = T diag(v) T^T is rank deficient
+        g.S_rest = g.S_rest[:0]
+        g.ev_rest = g.ev_rest[:0]
+    d = img.d
+    x0 = np.random.RandomState(1).uniform(0.2, 0.8, (16, d))
+    with DeviceEmulator(img) as dev:
+        s = DeviceStretchEnsemble(16, d, dev, seed=5)
+        with pytest.raises(ValueError, match="returned NaN"):
+            s.run_mcmc(x0, 5)

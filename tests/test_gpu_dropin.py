@@ -58,3 +58,27 @@ def test_log_posterior_module_is_a_drop_in(toy):
     assert abs(val - ref["ref_logp_rows"][i]) < 1e-9 * abs(ref["ref_logp_rows"][i])
     lp.close()
     emulation.clear_cache()
+
+
+def test_run_mcmc_device_and_host_samplers_agree(toy, tmp_path):
+    """mcmc.run_mcmc (mcmc.py:34-134): burn-in -> re-seed -> production with the ensemble on the GPU gives exactly the
+    chain of the host-side sampler calling the same log-posterior, and the reference's output keys."""
+    import types
+
+    from bayesian_inference_b200 import emulation, log_posterior as lp, mcmc
+
+    d = len(toy.min)
+    cfg = types.SimpleNamespace(
+        analysis_config={"parameterization": {"p": {"names": [f"p{i}" for i in range(d)], "min": list(toy.min), "max": list(toy.max)}}},
+        parameterization="p", analysis_name="toy", config_file="", output_dir=str(tmp_path), mcmc_output_dir=str(tmp_path),
+        n_walkers=16, n_burn_steps=40, n_sampling_steps=60, n_logging_steps=50, sampler_outputfile=None)
+    kw = dict(emulation_config=toy.emulation_config, emulation_results=toy.emulation_results,
+              experimental_results=toy.experimental_results, seed=12, write=False)
+    a = mcmc.run_mcmc(cfg, sampler="device", **kw)
+    b = mcmc.run_mcmc(cfg, sampler="host", **kw)
+    assert a["chain"].shape == (60, 16, d) and a["log_prob"].shape == (60, 16)
+    assert np.array_equal(a["chain"], b["chain"]) and np.array_equal(a["log_prob"], b["log_prob"])
+    assert np.array_equal(a["acceptance_fraction"], b["acceptance_fraction"])
+    assert np.all(np.isfinite(a["log_prob"])) and a["n_log_prob_rows"] == b["n_log_prob_rows"]
+    lp.close()
+    emulation.clear_cache()
