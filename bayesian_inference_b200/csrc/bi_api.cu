@@ -584,8 +584,8 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         CKB(cudaFuncSetAttribute(gp_predict_kernel<false, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
     }
     {
-        const size_t cs = (size_t)(2 * 32 * (std::max(h->K0, 4) + 1) + std::max(h->K0, 4)) * sizeof(double);
-        CKB(cudaFuncSetAttribute(cov_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(cs, 48 * 1024)));
+        const size_t cs = (size_t)std::max(h->K0, 4) * 33 * sizeof(double);
+        if (cs > 48 * 1024) CKB(cudaFuncSetAttribute(cov_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cs));
     }
     if (h->has_data) {
         h->chol_smem = chol_smem_bytes(Fp, h->K0);
@@ -686,11 +686,11 @@ static int predict_any(bi_handle h, int group, const double* theta, int64_t W, d
     CovParams P;
     if (group < 0) {
         P.Fo = h->F; P.K0 = h->K0; P.voff = 0; P.nq = h->Ptot; P.Trow = h->dTrow; P.Uc = h->dUblk;
-        P.mu = h->dMeanMerged; P.obs = h->dObs;
+        P.mu = h->dMeanMerged; P.obs = h->dObs; P.tile_omin = h->dTileOmin; P.tile_omax = h->dTileOmax;
     } else {
         const GroupImg& I = h->groups[group];
         P.Fo = I.Fg; P.K0 = I.K0g; P.voff = I.pc_off; P.nq = I.P; P.Trow = I.dTg; P.Uc = I.dUs; P.mu = I.dMean;
-        P.obs = nullptr;
+        P.obs = nullptr; P.tile_omin = nullptr; P.tile_omax = nullptr;
     }
     P.Ptot = h->Ptot; P.m = dM; P.v = dV; P.n_div = n_div; P.mean_out = mean_out; P.cov_out = cov_out; P.W = W;
     if (mean_out) {
@@ -700,7 +700,7 @@ static int predict_any(bi_handle h, int group, const double* theta, int64_t W, d
         CK(cudaGetLastError());
     }
     if (cov_out) {
-        const size_t smem = (size_t)(2 * 32 * (P.K0 + 1) + P.K0) * sizeof(double);
+        const size_t smem = (size_t)P.K0 * 33 * sizeof(double);     // v + the 32 x K0 operand tile (<= 48 KB for K0 <= 180)
         cov_assemble_kernel<<<dim3((P.Fo + 31) / 32, (unsigned)W), 256, smem, s>>>(P);
         h->launches++;
         CK(cudaGetLastError());

@@ -5,7 +5,7 @@
 //   :522-539  cov  = (S diag(v) S^T + U / n_div) * outer(scale, scale)
 //   :346-406  merge over groups: block diagonal per observable (mask), sorted-observable order
 //
-// The covariance is written to HBM here only because predict() returns it; the log-posterior path (chol_loglik.cuh)
+// The covariance is written to HBM here only because predict() returns it; the log-posterior path (chol_pipe.cuh)
 // never materialises it.  Bound: HBM writes, 8 F^2 bytes per walker.
 #pragma once
 #include "common.cuh"
@@ -22,6 +22,8 @@ struct CovParams {
     const double* Uc;     // (Fo, Fo) unexplained covariance already multiplied by outer(scale, scale) (and masked)
     const double* mu;     // (Fo) scaler mean
     const int* obs;       // (Fo) observable id per row, or nullptr (no mask: one emulation group on its own)
+    const int* tile_omin; // smallest / largest observable id of each 32-row tile (with obs), else nullptr
+    const int* tile_omax;
     const double* m;      // (W, Ptot)
     const double* v;      // (W, Ptot)
     double n_div;
@@ -40,49 +42,114 @@ __global__ void __launch_bounds__(256) mean_kernel(const CovParams P) {
     P.mean_out[idx] = s + __ldg(P.mu + r);
 }
 
-// grid (ceil(Fo/32), W), 256 threads; dynamic smem = (2 * 32 * (K0 + 1) + K0) doubles
-__global__ void __launch_bounds__(256) cov_assemble_kernel(const CovParams P) {
+// grid (ceil(Fo/32), W), 256 threads = 8 warps.  CTA (i, w) produces row tile i of walker w's covariance and, by
+// symmetry of T diag(v) T^T, the mirrored column tile: warp q takes the tiles j = q, q + 8, ... <= i, contracts
+// (T_i diag(v)) T_j^T on the FP64 tensor pipe (DMMA m8n8k4, operand fragments read straight from the row-major,
+// L1/L2-resident T) and writes tile (i, j) and its transpose (j, i), each with its own U entries.  Tiles whose
+// observables do not overlap (block-diagonal-per-observable merge, emulation.py:346-406) skip the contraction and
+// write zeros.  Half the flops of the full product, so the kernel is bound by its 8 F^2 bytes of HBM writes.
+__global__ void __launch_bounds__(256, 2) cov_assemble_kernel(const CovParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int K0 = P.K0, ld = K0 + 1;
-    double* sTi = reinterpret_cast<double*>(smem_raw);   // rows of tile i, pre-multiplied by v
-    double* sTj = sTi + 32 * ld;
-    double* sv = sTj + 32 * ld;
-    const int tid = threadIdx.x;
+    const int K0 = P.K0, nks = K0 >> 2;
+    double* sv = reinterpret_cast<double*>(smem_raw);
+    double* sA = sv + K0;                      // T_i diag(v), operand-fragment-major: [(mf * nks + ks) * 32 + lane]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3;
     const long long w = blockIdx.y;
-    const int i0 = blockIdx.x * 32;
+    const int it = blockIdx.x, i0 = it * 32;
     for (int q = tid; q < K0; q += 256) sv[q] = (q < P.nq) ? P.v[w * P.Ptot + P.voff + q] : 0.0;
     __syncthreads();
     for (int idx = tid; idx < 32 * K0; idx += 256) {
         const int r = idx / K0, q = idx - r * K0;
-        sTi[r * ld + q] = (i0 + r < P.Fo) ? __ldg(P.Trow + (long long)(i0 + r) * K0 + q) * sv[q] : 0.0;
+        sA[of_index(r, q, nks)] = (i0 + r < P.Fo) ? __ldg(P.Trow + (long long)(i0 + r) * K0 + q) * sv[q] : 0.0;
     }
-    const int c = tid & 31, r0 = tid >> 5;
-    const int ntl = (P.Fo + 31) / 32;
+    __syncthreads();
     double* out = P.cov_out + w * (long long)P.Fo * P.Fo;
-    for (int jt = 0; jt < ntl; ++jt) {
+    const int omin_i = P.tile_omin ? P.tile_omin[it] : 0;
+    const double rinv = 1.0 / P.n_div;         // U / n_div as a product: within 1 ulp of the reference's quotient
+    for (int jt = warp; jt <= it; jt += 8) {
         const int j0 = jt * 32;
-        __syncthreads();
-        for (int idx = tid; idx < 32 * K0; idx += 256) {
-            const int r = idx / K0, q = idx - r * K0;
-            sTj[r * ld + q] = (j0 + r < P.Fo) ? __ldg(P.Trow + (long long)(j0 + r) * K0 + q) : 0.0;
-        }
-        __syncthreads();
-        double acc[4] = {0.0, 0.0, 0.0, 0.0};
-        for (int q = 0; q < K0; ++q) {
-            const double b = sTj[c * ld + q];
+        double acc[4][4][2];
 #pragma unroll
-            for (int rr = 0; rr < 4; ++rr) acc[rr] = fma(sTi[(r0 + 8 * rr) * ld + q], b, acc[rr]);
-        }
-        const int col = j0 + c;
-        if (col < P.Fo) {
-            const int oc = P.obs ? P.obs[col] : 0;
+        for (int mf = 0; mf < 4; ++mf)
 #pragma unroll
-            for (int rr = 0; rr < 4; ++rr) {
-                const int row = i0 + r0 + 8 * rr;
+            for (int nf = 0; nf < 4; ++nf) acc[mf][nf][0] = acc[mf][nf][1] = 0.0;
+        const bool overlap = P.tile_omax ? (P.tile_omax[jt] >= omin_i) : true;
+        if (!overlap) {
+            // structurally zero tile and its mirror: plain zero fill, one 256-byte row segment per 16 lanes
+            const int rr = lane >> 4, cc = (lane & 15) * 2;
+#pragma unroll 4
+            for (int r = rr; r < 32; r += 2) {
+                const int row = i0 + r, col = j0 + cc;           // jt < it here, so col + 1 < Fo always
                 if (row < P.Fo) {
-                    const bool same = P.obs ? (P.obs[row] == oc) : true;
-                    const double u = __ldg(P.Uc + (long long)row * P.Fo + col) / P.n_div;
-                    out[(long long)row * P.Fo + col] = same ? acc[rr] + u : 0.0;
+                    out[(long long)row * P.Fo + col] = 0.0;
+                    out[(long long)row * P.Fo + col + 1] = 0.0;
+                }
+                const int mrow = j0 + r, mcol = i0 + cc;
+                if (mcol < P.Fo) out[(long long)mrow * P.Fo + mcol] = 0.0;
+                if (mcol + 1 < P.Fo) out[(long long)mrow * P.Fo + mcol + 1] = 0.0;
+            }
+            continue;
+        }
+        // operands: A = rows of T_i scaled by v (shared by the 8 warps: staged once in shared memory, fragment-major),
+        // B = rows of T_j read straight from the row-major, L1/L2-resident T (row index clamped, never predicated)
+        {
+            int rb[4];
+#pragma unroll
+            for (int nf = 0; nf < 4; ++nf) rb[nf] = min(j0 + nf * 8 + g, P.Fo - 1) * K0 + t;
+            for (int ks = 0; ks < nks; ++ks) {
+                double a[4], b[4];
+#pragma unroll
+                for (int mf = 0; mf < 4; ++mf) a[mf] = sA[(mf * nks + ks) * 32 + lane];
+#pragma unroll
+                for (int nf = 0; nf < 4; ++nf) b[nf] = __ldg(P.Trow + rb[nf] + ks * 4);
+#pragma unroll
+                for (int mf = 0; mf < 4; ++mf)
+#pragma unroll
+                    for (int nf = 0; nf < 4; ++nf) dmma(acc[mf][nf], a[mf], b[nf]);
+            }
+        }
+        int ocol[4][2];
+#pragma unroll
+        for (int nf = 0; nf < 4; ++nf)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) ocol[nf][e] = P.obs ? P.obs[min(j0 + nf * 8 + 2 * t + e, P.Fo - 1)] : 0;
+        const bool even = (P.Fo & 1) == 0;
+#pragma unroll
+        for (int mf = 0; mf < 4; ++mf) {
+            const int row = i0 + mf * 8 + g;
+            if (row >= P.Fo) continue;
+            const int orow = P.obs ? P.obs[row] : 0;
+            const double* Ur = P.Uc + (long long)row * P.Fo;
+            double* po = out + (long long)row * P.Fo;
+#pragma unroll
+            for (int nf = 0; nf < 4; ++nf) {
+                const int col = j0 + nf * 8 + 2 * t;        // columns col, col + 1
+                if (col >= P.Fo) continue;
+                const bool two = col + 1 < P.Fo;
+                const bool s0 = ocol[nf][0] == orow, s1 = two && ocol[nf][1] == orow;
+                double u0 = 0.0, u1 = 0.0;
+                if (two && even) {
+                    const double2 uu = __ldg(reinterpret_cast<const double2*>(Ur + col));   // row * Fo + col even: aligned
+                    u0 = uu.x;
+                    u1 = uu.y;
+                } else {
+                    u0 = __ldg(Ur + col);
+                    if (two) u1 = __ldg(Ur + col + 1);
+                }
+                const double o0 = s0 ? fma(u0, rinv, acc[mf][nf][0]) : 0.0;
+                const double o1 = s1 ? fma(u1, rinv, acc[mf][nf][1]) : 0.0;
+                if (two && even) {
+                    *reinterpret_cast<double2*>(po + col) = make_double2(o0, o1);
+                } else {
+                    po[col] = o0;
+                    if (two) po[col + 1] = o1;
+                }
+                if (jt < it) {                                                   // mirrored tile (j, i), its own U entries
+                    out[(long long)col * P.Fo + row] = s0 ? fma(__ldg(P.Uc + (long long)col * P.Fo + row), rinv, acc[mf][nf][0]) : 0.0;
+                    if (two)
+                        out[(long long)(col + 1) * P.Fo + row] =
+                            s1 ? fma(__ldg(P.Uc + (long long)(col + 1) * P.Fo + row), rinv, acc[mf][nf][1]) : 0.0;
                 }
             }
         }

@@ -221,6 +221,33 @@ class DeviceEmulator:
         return m, v
 
 
+    def kernel_vectors_tensor(self, group: int, theta):
+        """k (W, P_g, N_g) as a CUDA tensor (sklearn kernel_(X, X_train_) per PC); enqueues on torch's current stream."""
+        import torch
+
+        g = self.image.groups[group]
+        W = theta.shape[0]
+        out = torch.empty((W, g.n_pc, g.n_design), dtype=torch.float64, device=theta.device)
+        stream = torch.cuda.current_stream(theta.device).cuda_stream
+        self._check(self._lib.bi_kernel_vectors(self._h, group, C.c_void_p(theta.data_ptr()), W, C.c_void_p(out.data_ptr()),
+                                                C.c_void_p(stream)), "bi_kernel_vectors")
+        return out
+
+    def predict_tensor(self, theta, n_div: Optional[float] = None, want_cov: bool = True, mean=None, cov=None):
+        """Merged prediction on the device: mean (W, F), cov (W, F, F) CUDA tensors (emulation.predict without the copy back)."""
+        import torch
+
+        W, F = theta.shape[0], self.n_features
+        nd = float(W if n_div is None else n_div)
+        if mean is None:
+            mean = torch.empty((W, F), dtype=torch.float64, device=theta.device)
+        if want_cov and cov is None:
+            cov = torch.empty((W, F, F), dtype=torch.float64, device=theta.device)
+        stream = torch.cuda.current_stream(theta.device).cuda_stream
+        self._check(self._lib.bi_predict(self._h, C.c_void_p(theta.data_ptr()), W, nd, C.c_void_p(mean.data_ptr()),
+                                         C.c_void_p(cov.data_ptr()) if want_cov else None, C.c_void_p(stream)), "bi_predict")
+        return mean, cov
+
     # ---- stretch-move half-step on device-resident state (SURVEY §8 f1) ------------------------------------------
     def stretch_propose(self, coords, s_idx, c_idx, zz, q_out) -> None:
         """q_out[k] = c - (c - s) * zz[k]; all arguments CUDA tensors (coords f64 (W,d), indices int32 (ns), zz f64 (ns))."""

@@ -1,0 +1,58 @@
+"""Chain throughput of mcmc-style sampling: host-side stretch move calling the CUDA log-posterior once
+per half-step vs the device-resident sampler.  python tools/chain_bench.py [--workload C1] [--steps 500] [--mode dense]"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="C1")
+    ap.add_argument("--steps", type=int, default=500)
+    ap.add_argument("--walkers", type=int, default=0)
+    ap.add_argument("--mode", default="dense")
+    ap.add_argument("--block", type=int, default=64)
+    a = ap.parse_args()
+    import torch
+
+    from bayesian_inference_b200 import image, synthetic
+    from bayesian_inference_b200.device import DeviceEmulator
+    from bayesian_inference_b200.ensemble import DeviceStretchEnsemble, StretchEnsemble
+
+    spec = synthetic.config(a.workload)
+    if a.walkers:
+        spec.n_walkers = a.walkers
+    an = synthetic.generate(spec)
+    img = image.pack(an.emulation_config, an.emulation_results, min=an.min, max=an.max,
+                     experimental_results=an.experimental_results, sigma_exp=an.sigma_exp)
+    W, d = spec.n_walkers, spec.d
+    x0 = np.random.RandomState(1).uniform(0.3, 0.7, (W, d))
+    out = {"workload": spec.name, "walkers": W, "steps": a.steps, "mode": a.mode, "n_obs": img.n_features}
+    with DeviceEmulator(img, max_batch=W) as dev:
+        for name, mk in (("host", lambda: StretchEnsemble(W, d, lambda X: dev.log_posterior(X, n_div=1.0, mode=a.mode), seed=3)),
+                         ("device", lambda: DeviceStretchEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block))):
+            s = mk()
+            s.run_mcmc(x0, 10)             # warm-up
+            s = mk()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            s.run_mcmc(x0, a.steps)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            out[name] = {"seconds": dt, "steps_per_s": a.steps / dt, "evals_per_s": s.n_log_prob_rows / dt,
+                         "acceptance": float(s.acceptance_fraction.mean())}
+            out[name + "_chain_sum"] = float(np.sum(s.get_chain()))
+    out["identical_chain"] = out.pop("host_chain_sum") == out.pop("device_chain_sum")
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
