@@ -139,7 +139,7 @@ int ensure_out_scratch(bi_handle h, size_t bytes) {
 int build_a_tiles(bi_handle h, double n_div, cudaStream_t s) {
     if (h->a_ndiv == n_div) return 0;
     const int ntl = h->nt * (h->nt + 1) / 2;
-    build_a_tiles_kernel<<<ntl, 256, 0, s>>>(h->dSig, h->dYerr, h->dUblk, n_div, h->F, h->dATiles);
+    build_a_tiles_kernel<<<ntl, 256, 0, s>>>(h->dSig, h->dYerr, h->dUblk, n_div, h->F, h->chol_impl == 2 ? 1 : 0, h->dATiles);
     h->launches++;
     CK(cudaGetLastError());
     h->a_ndiv = n_div;
@@ -209,7 +209,7 @@ int launch_chol(bi_handle h, const double* dTheta, const double* dM, const doubl
             cudaMemsetAsync(dbg, 0, 64 * 8, s);
             PP.dbg = dbg;
 #endif
-            chol_pipe_kernel<false><<<grid, PIPE_THREADS, h->pipe_smem, s>>>(PP);
+            chol_pipe_kernel<<<grid, PIPE_THREADS, h->pipe_smem, s>>>(PP);
 #ifdef PIPE_TIMING
             {
                 long long hb[64];
@@ -343,7 +343,9 @@ int bi_create(const bi_desc* D, bi_handle* out) {
     h->sm_count = prop.multiProcessorCount;
     CKB(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     h->d = D->d; h->G = D->n_groups; h->B = D->n_blocks; h->F = D->n_features;
-    h->nt = (h->F + 31) / 32; h->Fp = h->nt * 32;
+    // one more row than F: row F of the factorised matrix is the augmented dY row of the pipelined kernel (chol_pipe.cuh);
+    // the v1 kernel sees it as one more identity padding row
+    h->nt = (h->F + 1 + 31) / 32; h->Fp = h->nt * 32;
     if (D->max_batch > 0) h->max_batch = D->max_batch;
     const int d = h->d, F = h->F, Fp = h->Fp, nt = h->nt;
     h->hMin.assign(D->prior_min, D->prior_min + d);
@@ -600,8 +602,8 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         h->pipe_smem = pipe_smem_bytes(Fp, h->nTc * 32);
         if (h->chol_impl == 2 && (h->pipe_smem > 227 * 1024 || nt > 120)) h->chol_impl = 1;
         if (h->chol_impl == 2) {
-            CKB(cudaFuncSetAttribute(chol_pipe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pipe_smem));
-            CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_pipe_kernel<false>, PIPE_THREADS, h->pipe_smem));
+            CKB(cudaFuncSetAttribute(chol_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pipe_smem));
+            CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_pipe_kernel, PIPE_THREADS, h->pipe_smem));
             if (occ < 1) {
                 h->err = "pipelined Cholesky kernel does not fit on an SM";
                 return bail(BI_E_UNSUPPORTED);

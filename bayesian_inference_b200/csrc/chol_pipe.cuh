@@ -146,7 +146,6 @@ __device__ __forceinline__ void half_chunk_mma(double (&acc)[2][4][2], const dou
             for (int nf = 0; nf < 4; ++nf) dmma(acc[mi][nf], a[mi], b[nf]);
     }
 }
-
 // X = C L_jj^-T for one 16 x 32 strip held as operand fragments a[mi][ks]; sLinv is [nf][ks][lane]
 __device__ __forceinline__ void strip_trsm(const double (&a)[2][8], double (&x)[2][4][2], const double* sLinvLane) {
 #pragma unroll
@@ -174,7 +173,10 @@ __device__ __forceinline__ void strip_trsm(const double (&a)[2][8], double (&x)[
 //   sLjj   [nf][ks][lane] operand-fragment-major L_jj (B operand of the blocked solve), upper part zero
 //   sLinvB [b][kk][lane]: (L_bb)^-1 of the four 8 x 8 diagonal blocks as B fragments
 // returns 0 or the 1-based index of the first non-positive pivot; adds sum(log L_ii) to logdet.
-__device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, double* sLinvB, double* sRinv, int lane, double& logdet) {
+// aug >= 0: row / column `aug` of this tile is the augmented dY row (see the kernel): its "pivot" is -|L^-1 dY|^2, which is
+// returned in quad and replaced by 1 so that the (identity) padding rows behind it factorise trivially.
+__device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, double* sLinvB, double* sRinv, int lane, double& logdet,
+                                                  int aug, double& quad) {
     const int g = lane >> 2, t = lane & 3;
     int bad = 0;
     double mypiv = 1.0;
@@ -185,7 +187,12 @@ __device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, doub
         for (int c = 0; c < 8; ++c) a[c] = sD[lane * 33 + 8 * b + c];
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
-            const double p = shfl_d(a[c], 8 * b + c);
+            double p = shfl_d(a[c], 8 * b + c);
+            if (8 * b + c == aug) {
+                quad = -p;
+                p = 1.0;
+                if (lane == aug) a[c] = 1.0;
+            }
             if (!(p > 0.0) && bad == 0) bad = 8 * b + c + 1;
             if (lane == 8 * b + c) mypiv = p;
             const double rinv = rsqrt(p);
@@ -285,7 +292,14 @@ __device__ __forceinline__ void strip_trsm_blocked(double (&c)[2][4][2], double 
     }
 }
 
-template <bool EXPLICIT>
+// The dY row rides inside the matrix: the factorised matrix is the (F+1) x (F+1) augmented
+//     M = [ C   dY ]        chol(M) = [ L                     0 ]
+//         [ dY' 0  ]                  [ (L^-1 dY)'   sqrt(-|L^-1 dY|^2) ]
+// so row F of the factor is z = L^-1 dY and the would-be pivot of that row is -z'z: the quadratic form falls out of the
+// last diagonal tile's factorisation (warp_potrf_blocked, aug) and costs no unit of its own -- the separate dY unit
+// per panel of the first version cost 9 % of the kernel (one more lock-step round on every fourth panel).
+// Row F lives in strip hA of the last row tile.  With structured skipping that strip is the only dense one: in panels
+// that do not couple to the last tile it is swept as a single extra unit, and it always starts at the panel's own kmin.
 __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipeParams PP) {
     const CholParams& P = PP.c;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -313,10 +327,11 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
     const int g = lane >> 2;
     const int t = lane & 3;
     const int nt = P.nt;
-    const int nTc = EXPLICIT ? 0 : PP.nTc;
+    const int nTc = PP.nTc;
+    const int ra = P.F - (nt - 1) * 32;   // augmented row inside the last tile
+    const int hA = ra >> 4;               // ... its strip
 
     double* wsL = P.ws + (long long)blockIdx.x * P.ws_stride;
-    double* wsZ = wsL + (long long)nt * (nt - 1) / 2 * TILE_ELEMS;
 
     if (tid == 0) {
         for (int s = 0; s < PIPE_STAGES; ++s) {
@@ -328,13 +343,12 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
         mbar_init(&bars[BAR_PANEL], PIPE_CONSUMERS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (!EXPLICIT)
-        for (int r = tid; r < P.Fp; r += PIPE_THREADS) sObs[r] = P.obs_id[r];
+    for (int r = tid; r < P.Fp; r += PIPE_THREADS) sObs[r] = P.obs_id[r];
     for (int r = tid; r < P.nt; r += PIPE_THREADS) {
         sKmin[r] = P.kmin[r];
         sImax[r] = P.imax[r];
-        sOmin[r] = EXPLICIT ? 0 : P.tile_omin[r];
-        sOmax[r] = EXPLICIT ? 0 : P.tile_omax[r];
+        sOmin[r] = P.tile_omin[r];
+        sOmax[r] = P.tile_omax[r];
     }
     __syncthreads();
 
@@ -345,7 +359,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
         __syncthreads();   // previous walker fully retired
         if (tid == 0) {
             int inside = 1;
-            if (!EXPLICIT && P.check_prior) {
+            if (P.check_prior) {
                 for (int k = 0; k < P.d; ++k) {
                     const double x = P.theta[w * P.d + k];
                     if (!(x > P.prior_min[k] && x < P.prior_max[k])) inside = 0;
@@ -354,12 +368,11 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             sFlag[0] = inside;
             sFlag[1] = 0;
         }
-        if (!EXPLICIT)
-            for (int q = tid; q < K0p; q += PIPE_THREADS) {
-                const bool ok = q < P.Ptot;
-                sM[q] = ok ? P.m[w * P.Ptot + q] : 0.0;
-                sNegV[q] = ok ? -P.v[w * P.Ptot + q] : 0.0;
-            }
+        for (int q = tid; q < K0p; q += PIPE_THREADS) {
+            const bool ok = q < P.Ptot;
+            sM[q] = ok ? P.m[w * P.Ptot + q] : 0.0;
+            sNegV[q] = ok ? -P.v[w * P.Ptot + q] : 0.0;
+        }
         __syncthreads();
         if (!sFlag[0]) {
             if (tid == 0) {
@@ -369,16 +382,17 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             continue;
         }
         for (int r = tid; r < P.Fp; r += PIPE_THREADS) {
-            double s;
-            if (EXPLICIT) {
-                s = (r < P.F) ? P.dy_x[w * P.F + r] : 0.0;
-            } else {
-                s = __ldg(P.e + r);
-                for (int q = 0; q < P.K0; ++q) s = fma(__ldg(P.Tt + (long long)q * P.Fp + r), sM[q], s);
-            }
+            double s = __ldg(P.e + r);
+            for (int q = 0; q < P.K0; ++q) s = fma(__ldg(P.Tt + (long long)q * P.Fp + r), sM[q], s);
             sDy[r] = s;
         }
         __syncthreads();
+
+        // unit q of panel j -> (row tile i, strip h): q < nreg regular, q == nreg the lone augmented strip
+#define PIPE_UNIT(q, nreg, j, i, h)                      \
+    const bool uaug_ = ((q) >= (nreg));                  \
+    const int i = uaug_ ? nt - 1 : (j) + ((q) >> 1);     \
+    const int h = uaug_ ? hA : ((q) & 1)
 
         if (warp == PIPE_CONSUMERS) {
             // =============================== producer ==========================================================
@@ -388,24 +402,27 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             for (int j = 0; j < nt; ++j, ++gp) {
                 const int i_hi = sImax[j];
                 const int nreg = 2 * (i_hi - j + 1);
-                const int nunits = nreg + 1;
+                const int nunits = nreg + (i_hi < nt - 1 ? 1 : 0);
+                const int qA = (i_hi < nt - 1) ? nreg : 2 * (nt - 1 - j) + hA;   // the unit holding the augmented row
+                const int kA = (j == nt - 1) ? 0 : sKmin[j];   // ... is dense: it starts where the panel does, and in the last
+                                                               // panel (whose column F is the row itself) at 0
                 const double* Bsrc = wsL + (size_t)j * (j - 1) / 2 * TILE_ELEMS;
                 const int bh = lane - PIPE_CONSUMERS;   // 0 / 1 on the B lanes
                 bool waited = false;
                 for (int r0 = 0; r0 < nunits; r0 += PIPE_CONSUMERS) {
                     const int nact = min(PIPE_CONSUMERS, nunits - r0);
-                    const bool first_z = (r0 == nreg);
-                    const int i_first = first_z ? nt : j + (r0 >> 1);
+                    const bool first_aug = (r0 == nreg);          // the round is the lone augmented strip: no T chunks
+                    const int i_first = first_aug ? nt - 1 : j + (r0 >> 1);
                     const int q = r0 + lane;
                     const bool has = lane < nact;
-                    const bool uz = has && (q == nreg);
-                    const int i = uz ? nt : j + (q >> 1);
-                    const int my_kmin = has ? sKmin[uz ? j : i] : 0x7fffffff;
-                    const bool my_need0 = !EXPLICIT && has && !uz && sOmax[j] >= sOmin[min(i, nt - 1)];
+                    PIPE_UNIT(q, nreg, j, i, h);
+                    const bool uz = has && uaug_;
+                    const int my_kmin = has ? ((q == qA) ? kA : sKmin[i]) : 0x7fffffff;
+                    const bool my_need0 = has && !uz && sOmax[j] >= sOmin[i];
                     // ---- T chunks (theta-dependent part of the covariance)
-                    if (!EXPLICIT && !first_z && sOmax[j] >= sOmin[i_first]) {
+                    if (!first_aug && sOmax[j] >= sOmin[i_first]) {
                         const uint32_t bytes = (uint32_t)((2 + __popc(__ballot_sync(0xffffffffu, my_need0))) * SUB_ELEMS * 8);
-                        const double* Asrc = PP.TmP + (size_t)min(i, nt - 1) * nTc * TILE_ELEMS + (q & 1) * STRIP_ELEMS;
+                        const double* Asrc = PP.TmP + (size_t)i * nTc * TILE_ELEMS + h * STRIP_ELEMS;
                         const double* Bt = PP.TmP + (size_t)j * nTc * TILE_ELEMS;
                         for (int c2 = 0; c2 < 2 * nTc; ++c2, ++it) {
                             const int s = it % PIPE_STAGES;
@@ -420,24 +437,10 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                         }
                     }
                     // ---- factor chunks k < j
-                    const bool z_in_round = nreg < r0 + PIPE_CONSUMERS;
-                    const int klo = sKmin[z_in_round ? j : i_first];
-                    const double* Asrc = uz ? wsZ : wsL + (size_t)i * (i - 1) / 2 * TILE_ELEMS + (q & 1) * STRIP_ELEMS;
-#if PIPE_PREFETCH > 0
-                    // pull the first chunks of this sweep into L2 (the factor of 296 walkers does not fit there)
-                    for (int k = klo; k < min(j, klo + PIPE_PREFETCH); ++k) {
-                        if (k >= my_kmin) bulk_prefetch_l2(Asrc + (size_t)k * TILE_ELEMS, STRIP_ELEMS * 8);
-                        if (bh == 0 || bh == 1) bulk_prefetch_l2(Bsrc + (size_t)k * TILE_ELEMS + bh * STRIP_ELEMS, STRIP_ELEMS * 8);
-                    }
-#endif
+                    const bool a_in_round = (qA >= r0) && (qA < r0 + PIPE_CONSUMERS);
+                    const int klo = a_in_round ? kA : sKmin[i_first];
+                    const double* Asrc = wsL + (size_t)i * (i - 1) / 2 * TILE_ELEMS + h * STRIP_ELEMS;
                     for (int k = klo; k < j; ++k) {
-#if PIPE_PREFETCH > 0
-                        if (k + PIPE_PREFETCH < j) {
-                            if (k + PIPE_PREFETCH >= my_kmin) bulk_prefetch_l2(Asrc + (size_t)(k + PIPE_PREFETCH) * TILE_ELEMS, STRIP_ELEMS * 8);
-                            if (bh == 0 || bh == 1)
-                                bulk_prefetch_l2(Bsrc + (size_t)(k + PIPE_PREFETCH) * TILE_ELEMS + bh * STRIP_ELEMS, STRIP_ELEMS * 8);
-                        }
-#endif
                         if (k == j - 1 && !waited) {
                             // block column j-1 was written by panel j-1's solves: wait for all of them
                             mbar_wait(&bars[BAR_PANEL], (gp - 1) & 1);
@@ -463,7 +466,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             }
         } else if (warp == PIPE_CONSUMERS + 1) {
             // =============================== factor warp ========================================================
-            double logdet = 0.0;
+            double logdet = 0.0, quad = 0.0;
             int first_bad = 0;
             uint32_t gp = gpanel;
 #ifdef PIPE_TIMING
@@ -473,7 +476,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             for (int j = 0; j < nt; ++j, ++gp) {
                 mbar_wait(&bars[BAR_DIAG], gp & 1);
                 TADD(7);
-                const int bad = warp_potrf_blocked(sD, sLinv, sLinvB, sRinv, lane, logdet);
+                const int bad = warp_potrf_blocked(sD, sLinv, sLinvB, sRinv, lane, logdet, j == nt - 1 ? ra : -1, quad);
                 TADD(6);
                 if (bad) {
                     if (first_bad == 0) first_bad = j * 32 + bad;
@@ -486,6 +489,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             }
             if (lane == 0) {
                 sRed[8] = logdet;
+                sRed[9] = quad;
                 sFlag[1] = first_bad;
             }
 #ifdef PIPE_TIMING
@@ -496,7 +500,6 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
 #endif
         } else {
             // =============================== consumers ==========================================================
-            double zpart = 0.0;
             uint32_t gp = gpanel;
 #ifdef PIPE_TIMING
             long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -505,7 +508,9 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             for (int j = 0; j < nt; ++j, ++gp) {
                 const int i_hi = sImax[j];
                 const int nreg = 2 * (i_hi - j + 1);
-                const int nunits = nreg + 1;
+                const int nunits = nreg + (i_hi < nt - 1 ? 1 : 0);
+                const int qA = (i_hi < nt - 1) ? nreg : 2 * (nt - 1 - j) + hA;
+                const int kA = (j == nt - 1) ? 0 : sKmin[j];
                 const int omin_j = sOmin[j];
                 const int omax_j = sOmax[j];
                 uint32_t deferred = 0;
@@ -513,19 +518,18 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                 for (int r0 = 0; r0 < nunits; r0 += PIPE_CONSUMERS, ++rnd) {
                     const int q = r0 + warp;
                     const bool active = q < nunits;
-                    const bool is_z = (q == nreg);
-                    const int i = is_z ? nt : j + (q >> 1);
-                    const int h = is_z ? 0 : (q & 1);
-                    const bool first_z = (r0 == nreg);
-                    const int i_first = first_z ? nt : j + (r0 >> 1);
+                    PIPE_UNIT(q, nreg, j, i, h);
+                    const bool is_aug = active && uaug_;
+                    const bool first_aug = (r0 == nreg);
+                    const int i_first = first_aug ? nt - 1 : j + (r0 >> 1);
                     double acc[2][4][2];
 #pragma unroll
                     for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
                         for (int nf = 0; nf < 4; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
 
-                    if (!EXPLICIT && !first_z && omax_j >= sOmin[i_first]) {
-                        const bool need0 = active && !is_z && omax_j >= sOmin[i];
+                    if (!first_aug && omax_j >= sOmin[i_first]) {
+                        const bool need0 = active && !is_aug && omax_j >= sOmin[i];
                         for (int c2 = 0; c2 < 2 * nTc; ++c2, ++it) {
                             const int s = it % PIPE_STAGES;
                             mbar_wait(&bars[BAR_FULL + s], (it / PIPE_STAGES) & 1);
@@ -551,9 +555,9 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                         }
                     }
                     {
-                        const bool z_in_round = nreg < r0 + PIPE_CONSUMERS;
-                        const int klo = sKmin[z_in_round ? j : i_first];
-                        const int my_klo = active ? sKmin[is_z ? j : i] : 0x7fffffff;
+                        const bool a_in_round = (qA >= r0) && (qA < r0 + PIPE_CONSUMERS);
+                        const int klo = a_in_round ? kA : sKmin[i_first];
+                        const int my_klo = active ? ((q == qA) ? kA : sKmin[i]) : 0x7fffffff;
                         for (int k2 = 2 * klo; k2 < 2 * j; ++k2, ++it) {
                             const int s = it % PIPE_STAGES;
                             mbar_wait(&bars[BAR_FULL + s], (it / PIPE_STAGES) & 1);
@@ -568,32 +572,8 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                         }
                     }
                     if (!active) { TADD(2); continue; }
-                    // ---- C = A_ij - acc
-                    if (is_z) {
-#pragma unroll
-                        for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-                            for (int nf = 0; nf < 4; ++nf)
-#pragma unroll
-                                for (int e = 0; e < 2; ++e) {
-                                    const double init = (mi == 0 && g == 0) ? sDy[j * 32 + nf * 8 + 2 * t + e] : 0.0;
-                                    acc[mi][nf][e] = init - acc[mi][nf][e];
-                                }
-                    } else if (EXPLICIT) {
-                        const double* Cw = P.cov_x + w * (long long)P.F * P.F;
-#pragma unroll
-                        for (int mi = 0; mi < 2; ++mi) {
-                            const int r = i * 32 + (2 * h + mi) * 8 + g;
-#pragma unroll
-                            for (int nf = 0; nf < 4; ++nf)
-#pragma unroll
-                                for (int e = 0; e < 2; ++e) {
-                                    const int cc = j * 32 + nf * 8 + 2 * t + e;
-                                    const double init = (r < P.F && cc < P.F) ? Cw[(long long)r * P.F + cc] : (r == cc ? 1.0 : 0.0);
-                                    acc[mi][nf][e] = init - acc[mi][nf][e];
-                                }
-                        }
-                    } else {
+                    // ---- C = A_ij - acc   (+ dY in the augmented row)
+                    {
                         const double2* At = reinterpret_cast<const double2*>(P.Atiles + ((long long)i * (i + 1) / 2 + j) * TILE_ELEMS);
 #pragma unroll
                         for (int mi = 0; mi < 2; ++mi)
@@ -603,8 +583,19 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                                 acc[mi][nf][0] = a0.x - acc[mi][nf][0];
                                 acc[mi][nf][1] = a0.y - acc[mi][nf][1];
                             }
+                        if (q == qA && g == (ra & 7)) {
+                            const int mA = (ra >> 3) & 1;
+#pragma unroll
+                            for (int mi = 0; mi < 2; ++mi)
+                                if (mi == mA) {
+#pragma unroll
+                                    for (int nf = 0; nf < 4; ++nf)
+#pragma unroll
+                                        for (int e = 0; e < 2; ++e) acc[mi][nf][e] += sDy[j * 32 + nf * 8 + 2 * t + e];
+                                }
+                        }
                     }
-                    if (!is_z && i == j) {
+                    if (i == j) {
 #pragma unroll
                         for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
@@ -616,8 +607,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                         TADD(2);
                         continue;
                     }
-                    double* Ct = (is_z ? wsZ + (long long)j * TILE_ELEMS : wsL + ((long long)i * (i - 1) / 2 + j) * TILE_ELEMS) +
-                                 h * STRIP_ELEMS + lane;
+                    double* Ct = wsL + ((long long)i * (i - 1) / 2 + j) * TILE_ELEMS + h * STRIP_ELEMS + lane;
                     if (!mbar_test(&bars[BAR_LINV], gp & 1)) {
                         // factor of the diagonal tile not there yet: park the strip, solve at the end of the panel
 #pragma unroll
@@ -634,10 +624,6 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                     {
                         double xa[2][8];
                         strip_trsm_blocked(acc, xa, sLinv + lane, sLinvB + lane, lane);
-                        if (is_z && g == 0) {
-#pragma unroll
-                            for (int nf = 0; nf < 4; ++nf) zpart += acc[0][nf][0] * acc[0][nf][0] + acc[0][nf][1] * acc[0][nf][1];
-                        }
 #pragma unroll
                         for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
@@ -651,11 +637,8 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                 for (int rr = 0; rr < rnd; ++rr) {
                     if (!((deferred >> rr) & 1)) continue;
                     const int q = rr * PIPE_CONSUMERS + warp;
-                    const bool is_z = (q == nreg);
-                    const int i = is_z ? nt : j + (q >> 1);
-                    const int h = is_z ? 0 : (q & 1);
-                    double* Ct = (is_z ? wsZ + (long long)j * TILE_ELEMS : wsL + ((long long)i * (i - 1) / 2 + j) * TILE_ELEMS) +
-                                 h * STRIP_ELEMS + lane;
+                    PIPE_UNIT(q, nreg, j, i, h);
+                    double* Ct = wsL + ((long long)i * (i - 1) / 2 + j) * TILE_ELEMS + h * STRIP_ELEMS + lane;
                     // the strip was parked as operand fragments; rebuild its accumulator fragments (inverse quad shuffle)
                     double x[2][4][2];
 #pragma unroll
@@ -672,10 +655,6 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                         }
                     double xa[2][8];
                     strip_trsm_blocked(x, xa, sLinv + lane, sLinvB + lane, lane);
-                    if (is_z && g == 0) {
-#pragma unroll
-                        for (int nf = 0; nf < 4; ++nf) zpart += x[0][nf][0] * x[0][nf][0] + x[0][nf][1] * x[0][nf][1];
-                    }
 #pragma unroll
                     for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
@@ -691,9 +670,8 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             if (PP.dbg && lane == 0)
                 for (int c = 0; c < 8; ++c) atomicAdd((unsigned long long*)&PP.dbg[warp * 8 + c], (unsigned long long)tacc[c]);
 #endif
-            const double zs = warp_sum(zpart);
-            if (lane == 0) sRed[warp] = zs;
         }
+#undef PIPE_UNIT
         gpanel += nt;
         __syncthreads();
         if (tid == 0) {
@@ -702,9 +680,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                 P.logp[w] = __longlong_as_double(0x7ff8000000000000LL);
                 if (P.info) P.info[w] = bad > P.F ? P.F : bad;
             } else {
-                double tot = 0.0;
-                for (int k = 0; k < PIPE_CONSUMERS; ++k) tot += sRed[k];
-                P.logp[w] = -0.5 * tot - sRed[8];
+                P.logp[w] = -0.5 * sRed[9] - sRed[8];
                 if (P.info) P.info[w] = 0;
             }
         }

@@ -75,11 +75,12 @@ __global__ void __launch_bounds__(256) unexplained_kernel(const double* __restri
     Us[(size_t)r * Fg + c] = s * (scale[r] * scale[c]);
 }
 
-// A = Sigma_exp + Ublk / n_div as accumulator-fragment-major lower tiles (index i(i+1)/2 + j); identity padding.
+// A = Sigma_exp + Ublk / n_div as accumulator-fragment-major lower tiles (index i(i+1)/2 + j); identity padding
+// (with aug != 0 the diagonal entry of row F is 0: the augmented dY row of the pipelined Cholesky kernel).
 // grid: (ntiles_lower), 256 threads (4 elements each).
 __global__ void __launch_bounds__(256) build_a_tiles_kernel(const double* __restrict__ Sig, const double* __restrict__ yerr,
                                                             const double* __restrict__ Ublk, double n_div, int F,
-                                                            double* __restrict__ out) {
+                                                            int aug, double* __restrict__ out) {
     // decode (i, j) from the linear lower-triangle index
     const int lin = blockIdx.x;
     int i = (int)((sqrt(8.0 * lin + 1.0) - 1.0) * 0.5);
@@ -96,7 +97,7 @@ __global__ void __launch_bounds__(256) build_a_tiles_kernel(const double* __rest
             else sg = (r == c) ? yerr[r] * yerr[r] : 0.0;
             val = sg + Ublk[(size_t)r * F + c] / n_div;
         } else {
-            val = (r == c) ? 1.0 : 0.0;
+            val = (r == c && !(aug && r == F)) ? 1.0 : 0.0;   // aug: M[F][F] = 0 (the dY row of chol_pipe.cuh)
         }
         out[(size_t)lin * 1024 + cf_index(rr, cc)] = val;
     }

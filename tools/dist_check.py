@@ -15,7 +15,7 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from bayesian_inference_b200 import image, synthetic  # noqa: E402
 from bayesian_inference_b200.device import DeviceEmulator  # noqa: E402
-from bayesian_inference_b200.ensemble import ShardedLogProb, StretchEnsemble  # noqa: E402
+from bayesian_inference_b200.ensemble import DeviceStretchEnsemble, ShardedLogProb, StretchEnsemble  # noqa: E402
 
 
 def main():
@@ -38,6 +38,11 @@ def main():
     lst = [torch.empty_like(chk) for _ in range(dist.get_world_size())]
     dist.all_gather(lst, chk)
     assert all(float(t) == float(chk) for t in lst), "ranks hold different chains"
+    # device-resident sampler, proposals sharded over the ranks, NCCL all-gather on the compute stream
+    ds = DeviceStretchEnsemble(100, img.d, dev, seed=42, block=20)
+    assert ds.world == dist.get_world_size()
+    ds.run_mcmc(a.theta, 50)
+    assert np.array_equal(ds.get_chain(), ref.get_chain()), "device-resident sharded chain != single-GPU chain"
     if rank == 0:
         print(f"dist_check ok: world={dist.get_world_size()} 100 walkers x 50 steps, acceptance {s.acceptance_fraction.mean():.3f}")
     dev.close()
