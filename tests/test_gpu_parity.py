@@ -120,6 +120,29 @@ def test_generated_config_vs_oracle(name, n_check, over):
             _cmp_logp(dev.log_posterior(th, n_div=1.0, mode="woodbury"), want)
 
 
+# ---- every alignment of the merged axis against the 32-row tiles (the dY row is row F of the factorised matrix) -----
+@pytest.mark.parametrize("n_obs,n_bins", [(1, 31), (2, 16), (3, 11), (7, 9), (4, 16), (3, 32), (1, 127), (5, 32), (9, 19)])
+def test_log_posterior_every_tile_alignment(n_obs, n_bins):
+    """F = 31, 32, 33, 63, 64, 96, 127, 160, 171: F % 32 == 0 adds a tile that holds only the augmented row, F % 32 == 31
+    puts it in the last row of the last tile, odd F exercises the unaligned covariance stores of predict()."""
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    spec = synthetic.ProblemSpec(f"align{n_obs}x{n_bins}", d=3, n_design=40, n_walkers=24, seed=n_obs * 100 + n_bins,
+                                 groups=[synthetic.GroupSpec("g0", 5, n_obs, n_bins)], oob_fraction=0.1)
+    a = synthetic.generate(spec)
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max,
+                     experimental_results=a.experimental_results)
+    z = img.to_flat()
+    want = cf.log_posterior(z, a.theta, n_div=1.0)
+    with DeviceEmulator(img) as dev:
+        for mode in ("dense", "structured", "woodbury"):
+            _cmp_logp(dev.log_posterior(a.theta, n_div=1.0, mode=mode), want)
+        mean, cov = dev.predict(a.theta[:5], n_div=1.0)
+        mo, co = cf.predict(z, a.theta[:5], n_div=1.0)
+        assert fro_err(mean, mo) < TOL_OBS and fro_err(cov, co) < TOL_OBS
+        assert np.array_equal(cov == 0.0, co == 0.0)
+
+
 # ---- size-independent properties at the full BASELINE size ----------------------------------------------------------
 @pytest.fixture(scope="module")
 def c3a():
