@@ -24,7 +24,7 @@ EXPORTS = [
     "bi_kernel_vectors", "bi_kernel_vectors_host", "bi_predict_pc", "bi_predict_pc_host",
     "bi_predict_group", "bi_predict_group_host", "bi_predict", "bi_predict_host",
     "bi_log_posterior", "bi_log_posterior_host", "bi_loglikelihood_host",
-    "bi_stretch_propose", "bi_stretch_accept",
+    "bi_stretch_propose", "bi_stretch_accept", "bi_set_data_sets", "bi_log_posterior_sets",
 ]
 
 MODE = {"dense": 0, "structured": 1, "woodbury": 2}
@@ -129,6 +129,8 @@ def load() -> C.CDLL:
     lib.bi_loglikelihood_host.argtypes = [h, dp, dp, i64, C.c_int32, dp, dp]
     lib.bi_stretch_propose.argtypes = [h, dp, dp, dp, dp, i64, dp, C.c_void_p]
     lib.bi_stretch_accept.argtypes = [h, dp, dp, dp, dp, dp, dp, dp, i64, dp, dp, C.c_void_p]
+    lib.bi_set_data_sets.argtypes = [h, C.c_int32, dp, dp]
+    lib.bi_log_posterior_sets.argtypes = [h, dp, dp, i64, C.c_double, C.c_int, dp, dp, C.c_void_p]
     for name in EXPORTS[8:]:
         getattr(lib, name).restype = C.c_int
     if lib.bi_abi_version() != 1:

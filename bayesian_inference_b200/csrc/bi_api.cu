@@ -51,6 +51,11 @@ struct bi_handle_s {
     int nTc = 0, chol_impl = 2;
     size_t pipe_smem = 0;
     double a_ndiv = -1.0;
+    // experimental data sets for batched closure tests (bi_set_data_sets)
+    int n_sets = 0;
+    double *dEsets = nullptr, *dYerrSets = nullptr, *dATilesSets = nullptr;
+    double sets_ndiv = -1.0;
+    std::vector<double> hMeanMerged;
     // Woodbury mode (allocated on first use)
     std::vector<std::array<long long, 4>> blk;   // observable blocks sorted by out_start: [group, out, in, len]
     std::vector<WbBlock> wbBlocks;
@@ -187,7 +192,7 @@ int launch_gp(bi_handle h, const double* dTheta, long long W, double* dM, double
 }
 
 int launch_chol(bi_handle h, const double* dTheta, const double* dM, const double* dV, long long W, int mode,
-                double* dLogp, int* dInfo, cudaStream_t s) {
+                double* dLogp, int* dInfo, cudaStream_t s, const int* dSetId = nullptr) {
     CholParams P;
     P.F = h->F; P.Fp = h->Fp; P.nt = h->nt; P.K0 = h->K0; P.nks0 = h->nks0; P.Ptot = h->Ptot; P.d = h->d;
     P.W = W; P.theta = dTheta; P.m = dM; P.v = dV; P.prior_min = h->dMin; P.prior_max = h->dMax;
@@ -196,7 +201,12 @@ int launch_chol(bi_handle h, const double* dTheta, const double* dM, const doubl
     P.kmin = (mode == BI_MODE_DENSE) ? h->dKminDense : h->dKminStruct;
     P.imax = (mode == BI_MODE_DENSE) ? h->dImaxDense : h->dImaxStruct;
     P.ws = h->dWs; P.ws_stride = h->ws_stride; P.logp = dLogp; P.info = dInfo; P.check_prior = 1;
-    P.cov_x = nullptr; P.dy_x = nullptr;
+    P.cov_x = nullptr; P.dy_x = nullptr; P.quad_out = nullptr; P.logdet_out = nullptr;
+    P.set_id = dSetId; P.e_stride = 0; P.a_stride = 0;
+    if (dSetId) {
+        P.e = h->dEsets; P.Atiles = h->dATilesSets;
+        P.e_stride = h->Fp; P.a_stride = (long long)h->nt * (h->nt + 1) / 2 * TILE_ELEMS;
+    }
     const int grid = (int)std::min<long long>(W, h->chol_ctas);
     {
         ProfScope ps(h, 1, s);
@@ -301,6 +311,9 @@ void bi_destroy(bi_handle h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (void* p : h->allocs) cudaFree(p);
     if (h->dOutScratch) cudaFree(h->dOutScratch);
+    if (h->dEsets) cudaFree(h->dEsets);
+    if (h->dYerrSets) cudaFree(h->dYerrSets);
+    if (h->dATilesSets) cudaFree(h->dATilesSets);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -519,6 +532,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
             TRY(upload(h, &h->dTmP, tmp.data(), tmp.size()));
         }
         TRY(upload(h, &h->dMeanMerged, mean.data(), mean.size()));
+        h->hMeanMerged = mean;
         TRY(upload(h, &h->dE, ev.data(), ev.size()));
         CKB(cudaStreamSynchronize(h->stream));
     }
@@ -1034,6 +1048,60 @@ int bi_stretch_accept(bi_handle h, double* coords, double* logp, const int32_t* 
         coords, logp, s_idx, q, new_lp, factors, logu, ns, h->d, reinterpret_cast<long long*>(n_accepted), nan_flag);
     h->launches++;
     CK(cudaGetLastError());
+    return 0;
+}
+
+// ---- several experimental data sets on one emulator image (closure tests) --------------------------------
+int bi_set_data_sets(bi_handle h, int32_t n_sets, const double* y, const double* y_err) {
+    if (!h || n_sets <= 0 || !y || !y_err) return fail(h, BI_E_ARG, "bad argument");
+    if (!h->has_data) return fail(h, BI_E_STATE, "handle was created without experimental data (scratch is sized by it)");
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());          // earlier calls may still read the previous sets on a caller's stream
+    for (double** p : {&h->dEsets, &h->dYerrSets, &h->dATilesSets})
+        if (*p) { cudaFree(*p); *p = nullptr; }
+    const int F = h->F, Fp = h->Fp;
+    std::vector<double> e((size_t)n_sets * Fp, 0.0);
+    for (int c = 0; c < n_sets; ++c)
+        for (int r = 0; r < F; ++r) e[(size_t)c * Fp + r] = h->hMeanMerged[r] - y[(size_t)c * F + r];
+    const size_t atile = (size_t)h->nt * (h->nt + 1) / 2 * TILE_ELEMS;
+    CK(cudaMalloc(&h->dEsets, e.size() * 8));
+    CK(cudaMalloc(&h->dYerrSets, (size_t)n_sets * F * 8));
+    CK(cudaMalloc(&h->dATilesSets, (size_t)n_sets * atile * 8));
+    CK(cudaMemcpy(h->dEsets, e.data(), e.size() * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(h->dYerrSets, y_err, (size_t)n_sets * F * 8, cudaMemcpyHostToDevice));
+    h->n_sets = n_sets;
+    h->sets_ndiv = -1.0;
+    return 0;
+}
+
+int bi_log_posterior_sets(bi_handle h, const double* theta, const int32_t* set_id, int64_t W, double n_div, int mode,
+                          double* logp_out, int32_t* info_out, void* stream) {
+    if (!h || !theta || !set_id || !logp_out || W < 0) return fail(h, BI_E_ARG, "bad argument");
+    if (h->n_sets <= 0) return fail(h, BI_E_STATE, "bi_set_data_sets has not been called");
+    if (!(n_div > 0.0)) return fail(h, BI_E_ARG, "data sets need an explicit n_div (1 for MCMC)");
+    if (mode != BI_MODE_DENSE && mode != BI_MODE_STRUCTURED)
+        return fail(h, BI_E_UNSUPPORTED, "data sets support the dense and structured modes");
+    if (W == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (h->sets_ndiv != n_div) {
+        const int ntl = h->nt * (h->nt + 1) / 2;
+        for (int c = 0; c < h->n_sets; ++c) {
+            build_a_tiles_kernel<<<ntl, 256, 0, s>>>(nullptr, h->dYerrSets + (size_t)c * h->F, h->dUblk, n_div, h->F,
+                                                     h->chol_impl == 2 ? 1 : 0, h->dATilesSets + (size_t)c * ntl * TILE_ELEMS);
+            h->launches++;
+        }
+        CK(cudaGetLastError());
+        h->sets_ndiv = n_div;
+    }
+    for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
+        const long long wb = std::min<long long>(h->max_batch, W - w0);
+        int rc = launch_gp(h, theta + w0 * h->d, wb, h->dM, h->dV, s);
+        if (rc) return rc;
+        rc = launch_chol(h, theta + w0 * h->d, h->dM, h->dV, wb, mode, logp_out + w0, info_out ? info_out + w0 : nullptr, s,
+                         set_id + w0);
+        if (rc) return rc;
+    }
     return 0;
 }
 

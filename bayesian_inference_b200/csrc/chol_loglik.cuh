@@ -49,6 +49,10 @@ struct CholParams {
     // EXPLICIT instantiation only (log_posterior._loglikelihood(y, cov), log_posterior.py:104):
     const double* cov_x;      // (W, F, F) row-major, lower triangle read
     const double* dy_x;       // (W, F)
+    // several experimental data sets on one emulator image (closure tests, steer_analysis.py:168-183): walker w uses
+    // e + set_id[w] * e_stride and Atiles + set_id[w] * a_stride; set_id == nullptr -> the handle's own data
+    const int* set_id;
+    long long e_stride, a_stride;
     double* quad_out;         // optional (W): dy^T C^-1 dy on its own (Woodbury combine), else nullptr
     double* logdet_out;       // optional (W): sum log diag chol(C)
 };
@@ -189,7 +193,7 @@ __global__ void __launch_bounds__(CHOL_THREADS, CHOL_MIN_BLOCKS) chol_loglik_ker
             if (EXPLICIT) {
                 s = (r < P.F) ? P.dy_x[w * P.F + r] : 0.0;
             } else {
-                s = __ldg(P.e + r);
+                s = __ldg(P.e + (P.set_id ? P.set_id[w] * P.e_stride : 0) + r);
                 for (int q = 0; q < P.K0; ++q) s = fma(__ldg(P.Tt + (long long)q * P.Fp + r), sM[q], s);
             }
             sDy[r] = s;
@@ -300,7 +304,7 @@ __global__ void __launch_bounds__(CHOL_THREADS, CHOL_MIN_BLOCKS) chol_loglik_ker
                     }
                 } else {
                     const double2* At = reinterpret_cast<const double2*>(
-                        P.Atiles + ((long long)i * (i + 1) / 2 + j) * TILE_ELEMS);
+                        P.Atiles + (P.set_id ? P.set_id[w] * P.a_stride : 0) + ((long long)i * (i + 1) / 2 + j) * TILE_ELEMS);
 #pragma unroll
                     for (int mi = 0; mi < 2; ++mi)
 #pragma unroll

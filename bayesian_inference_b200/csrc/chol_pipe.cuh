@@ -381,8 +381,11 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             }
             continue;
         }
+        const long long sid = P.set_id ? P.set_id[w] : 0;     // experimental data set of this walker
+        const double* e_w = P.e + sid * P.e_stride;
+        const double* At_w = P.Atiles + sid * P.a_stride;
         for (int r = tid; r < P.Fp; r += PIPE_THREADS) {
-            double s = __ldg(P.e + r);
+            double s = __ldg(e_w + r);
             for (int q = 0; q < P.K0; ++q) s = fma(__ldg(P.Tt + (long long)q * P.Fp + r), sM[q], s);
             sDy[r] = s;
         }
@@ -574,7 +577,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                     if (!active) { TADD(2); continue; }
                     // ---- C = A_ij - acc   (+ dY in the augmented row)
                     {
-                        const double2* At = reinterpret_cast<const double2*>(P.Atiles + ((long long)i * (i + 1) / 2 + j) * TILE_ELEMS);
+                        const double2* At = reinterpret_cast<const double2*>(At_w + ((long long)i * (i + 1) / 2 + j) * TILE_ELEMS);
 #pragma unroll
                         for (int mi = 0; mi < 2; ++mi)
 #pragma unroll

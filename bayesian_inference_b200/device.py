@@ -248,6 +248,41 @@ class DeviceEmulator:
                                          C.c_void_p(cov.data_ptr()) if want_cov else None, C.c_void_p(stream)), "bi_predict")
         return mean, cov
 
+    # ---- several experimental data sets on one image (closure tests) -----------------------------------
+    def set_data_sets(self, y, y_err) -> int:
+        """Load n pseudo-data sets (n, F) side by side; Sigma_exp = diag(y_err**2) per set.  Returns n."""
+        y, y_err = _f64(np.atleast_2d(y)), _f64(np.atleast_2d(y_err))
+        if y.shape != y_err.shape or y.shape[1] != self.n_features:
+            raise ValueError(f"y / y_err must both be (n_sets, {self.n_features})")
+        self._check(self._lib.bi_set_data_sets(self._h, y.shape[0], _ptr(y), _ptr(y_err)), "bi_set_data_sets")
+        self.n_sets = y.shape[0]
+        return self.n_sets
+
+    def log_posterior_sets_tensor(self, theta, set_id, n_div: float = 1.0, mode: str = "dense", out=None):
+        """Row w of theta is evaluated against data set set_id[w] (int32 CUDA tensor); enqueues on torch's current stream."""
+        import torch
+
+        W = theta.shape[0]
+        if not (theta.is_cuda and theta.dtype == torch.float64 and theta.is_contiguous() and set_id.is_cuda
+                and set_id.dtype == torch.int32 and set_id.is_contiguous() and set_id.shape[0] == W):
+            raise ValueError("theta: contiguous float64 CUDA (W, d); set_id: contiguous int32 CUDA (W)")
+        if out is None:
+            out = torch.empty(W, dtype=torch.float64, device=theta.device)
+        stream = torch.cuda.current_stream(theta.device).cuda_stream
+        self._check(self._lib.bi_log_posterior_sets(self._h, C.c_void_p(theta.data_ptr()), C.c_void_p(set_id.data_ptr()), W,
+                                                    float(n_div), _lib.MODE[mode], C.c_void_p(out.data_ptr()), None,
+                                                    C.c_void_p(stream)), "bi_log_posterior_sets")
+        return out
+
+    def log_posterior_sets(self, theta, set_id, n_div: float = 1.0, mode: str = "dense") -> np.ndarray:
+        import torch
+
+        th = torch.from_numpy(self._theta(theta)).cuda(self.device)
+        sid = torch.from_numpy(np.ascontiguousarray(set_id, dtype=np.int32)).cuda(self.device)
+        if sid.numel() and (int(sid.min()) < 0 or int(sid.max()) >= getattr(self, "n_sets", 0)):
+            raise ValueError("set_id out of range")
+        return self.log_posterior_sets_tensor(th, sid, n_div=n_div, mode=mode).cpu().numpy()
+
     # ---- stretch-move half-step on device-resident state (SURVEY §8 f1) ------------------------------------------
     def stretch_propose(self, coords, s_idx, c_idx, zz, q_out) -> None:
         """q_out[k] = c - (c - s) * zz[k]; all arguments CUDA tensors (coords f64 (W,d), indices int32 (ns), zz f64 (ns))."""

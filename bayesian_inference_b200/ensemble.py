@@ -158,23 +158,28 @@ def draw_stretch_randoms(rng: np.random.RandomState, nwalkers: int, ndim: int, n
     accept test compares exactly the numbers the host sampler compares.
     """
     W, ns = nwalkers, nwalkers // 2
-    out = {"s_idx": np.empty((nsteps, 2, ns), np.int32), "c_idx": np.empty((nsteps, 2, ns), np.int32),
-           "zz": np.empty((nsteps, 2, ns)), "factors": np.empty((nsteps, 2, ns)), "logu": np.empty((nsteps, 2, ns))}
-    all_inds = np.arange(W)
+    # the loop only draws (the order of the draws is what must be preserved); everything else is vectorised after it
+    inds_all = np.empty((nsteps, W), np.int64)
+    u_zz, u_acc = np.empty((nsteps, 2, ns)), np.empty((nsteps, 2, ns))
+    rint = np.empty((nsteps, 2, ns), np.int64)
+    base = np.arange(W) % 2
     for t in range(nsteps):
         rng.random_sample()
-        inds = all_inds % 2
+        inds = base.copy()
         rng.shuffle(inds)
+        inds_all[t] = inds
         for split in range(2):
-            S1 = inds == split
-            s_ids, c_ids = all_inds[S1], all_inds[~S1]
-            zz = ((a - 1.0) * rng.rand(ns) + 1.0) ** 2.0 / a
-            rint = rng.randint(c_ids.shape[0], size=(ns,))
-            with np.errstate(divide="ignore"):
-                logu = np.log(rng.rand(ns))
-            out["s_idx"][t, split], out["c_idx"][t, split] = s_ids, c_ids[rint]
-            out["zz"][t, split], out["factors"][t, split], out["logu"][t, split] = zz, (ndim - 1.0) * np.log(zz), logu
-    return out
+            u_zz[t, split] = rng.rand(ns)
+            rint[t, split] = rng.randint(W - ns, size=(ns,))
+            u_acc[t, split] = rng.rand(ns)
+    ids = [np.nonzero(inds_all == split)[1].reshape(nsteps, ns) for split in range(2)]   # walkers of each half, ascending
+    s_idx = np.stack([ids[0], ids[1]], axis=1)
+    c_ids = np.stack([ids[1], ids[0]], axis=1)
+    zz = ((a - 1.0) * u_zz + 1.0) ** 2.0 / a
+    with np.errstate(divide="ignore"):
+        logu = np.log(u_acc)
+    return {"s_idx": s_idx.astype(np.int32), "c_idx": np.take_along_axis(c_ids, rint, axis=2).astype(np.int32),
+            "zz": zz, "factors": (ndim - 1.0) * np.log(zz), "logu": logu}
 
 
 class DeviceStretchEnsemble(StretchEnsemble):
@@ -246,9 +251,9 @@ class DeviceStretchEnsemble(StretchEnsemble):
             n_acc = torch.zeros(W, dtype=torch.int64, device=device)
             nan_flag = torch.zeros(1, dtype=torch.int32, device=device)
             done = 0
+            r = draw_stretch_randoms(self._random, W, nd, min(self.block, iterations), self.a)
             while done < iterations:
                 nb = min(self.block, iterations - done)
-                r = draw_stretch_randoms(self._random, W, nd, nb, self.a)
                 rd = {k: torch.from_numpy(v).pin_memory().to(device, non_blocking=True) for k, v in r.items()}
                 chain_b = torch.empty((nb, W, nd), dtype=torch.float64, device=device)
                 lp_b = torch.empty((nb, W), dtype=torch.float64, device=device)
@@ -261,6 +266,8 @@ class DeviceStretchEnsemble(StretchEnsemble):
                                                 n_acc, nan_flag)
                     chain_b[t].copy_(coords)
                     lp_b[t].copy_(logp)
+                if done + nb < iterations:      # the next block's random numbers are drawn while the GPU runs this one
+                    r = draw_stretch_randoms(self._random, W, nd, min(self.block, iterations - done - nb), self.a)
                 chain_h, lp_h = chain_b.cpu().numpy(), lp_b.cpu().numpy()      # synchronises: the block is done
                 if int(nan_flag.item()):
                     raise ValueError("Probability function returned NaN")
@@ -272,6 +279,98 @@ class DeviceStretchEnsemble(StretchEnsemble):
                     self._log_prob.append(lp_h[t])
                     yield chain_h[t], lp_h[t]
                 done += nb
+
+
+class BatchedClosureEnsemble:
+    """Several independent ensembles advanced in lock-step on one GPU, chain c against experimental data set c
+    (SURVEY §8 f3).  The reference runs its closure tests -- one MCMC per validation design point, each against that
+    point's pseudo-data and the same emulators -- one after the other (steer_analysis.py:168-183); here every half-step
+    is one ``bi_stretch_propose`` / ``bi_log_posterior_sets`` / ``bi_stretch_accept`` over the walkers of all chains.
+    Chain c consumes its own ``RandomState`` exactly as a stand-alone run would, so it IS the stand-alone chain.
+
+    ``chains[c]`` is a ``StretchEnsemble`` used as the per-chain store (``get_chain``, ``flatchain``,
+    ``acceptance_fraction``, ``get_autocorr_time``, ``reset``).
+    """
+
+    def __init__(self, nwalkers: int, ndim: int, device_emulator, random_states, mode: str = "dense", a: float = 2.0,
+                 block: int = 64):
+        self.dev, self.mode, self.block, self.a = device_emulator, mode, int(block), float(a)
+        self.nwalkers, self.ndim, self.n_chains = int(nwalkers), int(ndim), len(random_states)
+        if getattr(device_emulator, "n_sets", 0) < self.n_chains:
+            raise ValueError("load one experimental data set per chain first (DeviceEmulator.set_data_sets)")
+        self.chains = [StretchEnsemble(nwalkers, ndim, None, a=a, random_state=rs) for rs in random_states]
+        self.n_log_prob_rows = 0
+
+    def reset(self) -> None:
+        for c in self.chains:
+            c.reset()
+
+    def run_mcmc(self, initial_states, nsteps: int):
+        """initial_states: (n_chains, W, d).  Returns the last coordinates (n_chains, W, d)."""
+        import torch
+
+        C_, W, nd, ns = self.n_chains, self.nwalkers, self.ndim, self.nwalkers // 2
+        x0 = np.array(initial_states, dtype=np.float64, copy=True)
+        if x0.shape != (C_, W, nd):
+            raise ValueError("incompatible input dimensions")
+        for c in range(C_):
+            if np.linalg.cond(np.cov(x0[c], rowvar=False).reshape(nd, nd)) > 1e8:
+                raise ValueError("Initial state has a large condition number. Make sure that your walkers are linearly independent.")
+        device = torch.device("cuda", self.dev.device)
+        with torch.cuda.device(device):
+            coords = torch.from_numpy(x0.reshape(C_ * W, nd)).to(device)
+            logp = torch.empty(C_ * W, dtype=torch.float64, device=device)
+            set_all = torch.arange(C_, dtype=torch.int32, device=device).repeat_interleave(W).contiguous()
+            set_q = torch.arange(C_, dtype=torch.int32, device=device).repeat_interleave(ns).contiguous()
+            self.dev.log_posterior_sets_tensor(coords, set_all, n_div=1.0, mode=self.mode, out=logp)
+            self.n_log_prob_rows += C_ * W
+            if bool(torch.isnan(logp).any()):
+                raise ValueError("Probability function returned NaN")
+            q = torch.empty((C_ * ns, nd), dtype=torch.float64, device=device)
+            new_lp = torch.empty(C_ * ns, dtype=torch.float64, device=device)
+            n_acc = torch.zeros(C_ * W, dtype=torch.int64, device=device)
+            nan_flag = torch.zeros(1, dtype=torch.int32, device=device)
+            def draw(nb):
+                per = [draw_stretch_randoms(ch._random, W, nd, nb, self.a) for ch in self.chains]
+                r = {}
+                for k in per[0]:
+                    off = (lambda c: c * W) if k in ("s_idx", "c_idx") else (lambda c: 0)
+                    r[k] = np.ascontiguousarray(np.concatenate([per[c][k] + off(c) for c in range(C_)], axis=2).astype(per[0][k].dtype))
+                return r
+
+            done = 0
+            r = draw(min(self.block, nsteps))
+            while done < nsteps:
+                nb = min(self.block, nsteps - done)
+                rd = {k: torch.from_numpy(v).pin_memory().to(device, non_blocking=True) for k, v in r.items()}
+                chain_b = torch.empty((nb, C_ * W, nd), dtype=torch.float64, device=device)
+                lp_b = torch.empty((nb, C_ * W), dtype=torch.float64, device=device)
+                for t in range(nb):
+                    for split in range(2):
+                        s_idx = rd["s_idx"][t, split]
+                        self.dev.stretch_propose(coords, s_idx, rd["c_idx"][t, split], rd["zz"][t, split], q)
+                        self.dev.log_posterior_sets_tensor(q, set_q, n_div=1.0, mode=self.mode, out=new_lp)
+                        self.dev.stretch_accept(coords, logp, s_idx, q, new_lp, rd["factors"][t, split], rd["logu"][t, split],
+                                                n_acc, nan_flag)
+                    chain_b[t].copy_(coords)
+                    lp_b[t].copy_(logp)
+                self.n_log_prob_rows += nb * 2 * C_ * ns
+                if done + nb < nsteps:          # drawn while the GPU runs this block
+                    r = draw(min(self.block, nsteps - done - nb))
+                chain_h = chain_b.cpu().numpy().reshape(nb, C_, W, nd)
+                lp_h = lp_b.cpu().numpy().reshape(nb, C_, W)
+                if int(nan_flag.item()):
+                    raise ValueError("Probability function returned NaN")
+                acc_h = n_acc.cpu().numpy().reshape(C_, W)
+                n_acc.zero_()
+                for c, ch in enumerate(self.chains):
+                    ch._accepted += acc_h[c]
+                    for t in range(nb):
+                        ch.iteration += 1
+                        ch._chain.append(chain_h[t, c])
+                        ch._log_prob.append(lp_h[t, c])
+                done += nb
+            return coords.cpu().numpy().reshape(C_, W, nd)
 
 
 class ShardedLogProb:

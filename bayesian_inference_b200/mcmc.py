@@ -27,7 +27,7 @@ from typing import Any, Optional
 import numpy as np
 
 from . import log_posterior
-from .ensemble import DeviceStretchEnsemble, ShardedLogProb, StretchEnsemble
+from .ensemble import BatchedClosureEnsemble, DeviceStretchEnsemble, ShardedLogProb, StretchEnsemble
 
 logger = logging.getLogger(__name__)
 
@@ -137,3 +137,48 @@ def run_mcmc(config, closure_index: int = -1, *, emulation_config=None, emulatio
     output_dict["n_log_prob_rows"] = sampler.n_log_prob_rows
     logger.info("Done.")
     return output_dict
+
+
+def run_mcmc_closures(config, pseudodata, *, emulation_config, emulation_results, design_points=None, seeds=None,
+                      mode: str = "dense", sigma_exp: Optional[np.ndarray] = None) -> list[dict[str, Any]]:
+    """All closure tests of an analysis at once.
+
+    The reference loops ``for i in validation_indices: mcmc.run_mcmc(config, closure_index=i)`` (steer_analysis.py:168-183):
+    one full MCMC per validation design point against that point's pseudo-data (``data_IO.data_array_from_h5(...,
+    pseudodata_index=i)``, data_IO.py:362-372), always with the same emulators.  Here the pseudo-data sets are loaded side
+    by side (``bi_set_data_sets``) and the chains advance in lock-step, one batched log-posterior call per half-step.
+    ``pseudodata``: list of ``{'y': (F,), 'y_err': (F,)}``; ``seeds[i]`` seeds chain i, which is then exactly the chain
+    ``run_mcmc(config, closure_index=i, seed=seeds[i])`` produces.  Returns one reference-style output dictionary per
+    closure test (nothing is written).
+    """
+    par = config.analysis_config["parameterization"][config.parameterization]
+    lo, hi = np.asarray(par["min"], dtype=np.float64), np.asarray(par["max"], dtype=np.float64)
+    ndim, W, C_ = len(par["names"]), config.n_walkers, len(pseudodata)
+    seeds = list(range(C_)) if seeds is None else list(seeds)
+    log_posterior.initialize_pool_variables(lo, hi, emulation_config, emulation_results, pseudodata[0], None,
+                                            sigma_exp=sigma_exp, mode=mode)
+    dev = log_posterior.device()
+    dev.set_data_sets(np.stack([np.asarray(p["y"], dtype=np.float64) for p in pseudodata]),
+                      np.stack([np.asarray(p["y_err"], dtype=np.float64) for p in pseudodata]))
+    rngs = [np.random.RandomState(sd) for sd in seeds]
+    ens = BatchedClosureEnsemble(W, ndim, dev, rngs, mode=mode)
+    start = np.stack([rng.uniform(lo, hi, (W, ndim)) for rng in rngs])                               # mcmc.py:88, per chain
+    nburn0 = config.n_burn_steps // 2
+    ens.run_mcmc(start, nburn0)
+    X0 = np.stack([c.flatchain[np.unique(c.flatlnprobability, return_index=True)[1][-W:]] for c in ens.chains])   # mcmc.py:99
+    ens.reset()
+    X0 = ens.run_mcmc(X0, config.n_burn_steps - nburn0)
+    ens.reset()
+    ens.run_mcmc(X0, config.n_sampling_steps)
+    out = []
+    for i, c in enumerate(ens.chains):
+        d: dict[str, Any] = {"chain": c.get_chain(), "acceptance_fraction": c.acceptance_fraction, "log_prob": c.get_log_prob()}
+        try:
+            d["autocorrelation_time"] = c.get_autocorr_time()
+        except Exception as e:
+            d["autocorrelation_time"] = None
+            logger.info(f"Could not compute autocorrelation time: {str(e)}")
+        d["design_point"] = None if design_points is None else design_points[i]
+        d["experimental_pseudodata"] = pseudodata[i]
+        out.append(d)
+    return out

@@ -166,6 +166,19 @@ int bi_stretch_accept(bi_handle h, double* coords, double* logp, const int32_t* 
                       const double* new_lp, const double* factors, const double* logu, int64_t ns,
                       int64_t* n_accepted, int32_t* nan_flag, void* stream);
 
+/* ---- several experimental data sets on one emulator image (closure tests, steer_analysis.py:168-183) ----------------
+ * The reference validates an analysis by running one MCMC per validation design point, each against that point's
+ * pseudo-data (data_IO.py:362-372) and the SAME emulators, one after the other.  Here the pseudo-data sets are loaded
+ * side by side and every walker names the set it is evaluated against, so all closure chains advance in one call.
+ *
+ * bi_set_data_sets: y, y_err (n_sets, F) HOST pointers, Sigma_exp = diag(y_err^2) per set; replaces earlier sets.
+ *                   The handle must have been created with experimental data (it sizes the scratch buffers).
+ * bi_log_posterior_sets: as bi_log_posterior with set_id (W) int32 DEVICE pointer, values in [0, n_sets);
+ *                   n_div must be given (> 0; 1 for MCMC); modes BI_MODE_DENSE and BI_MODE_STRUCTURED. */
+int bi_set_data_sets(bi_handle h, int32_t n_sets, const double* y, const double* y_err);
+int bi_log_posterior_sets(bi_handle h, const double* theta, const int32_t* set_id, int64_t W, double n_div, int mode,
+                          double* logp_out, int32_t* info_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -82,3 +82,41 @@ def test_run_mcmc_device_and_host_samplers_agree(toy, tmp_path):
     assert np.all(np.isfinite(a["log_prob"])) and a["n_log_prob_rows"] == b["n_log_prob_rows"]
     lp.close()
     emulation.clear_cache()
+
+
+def test_batched_closure_tests_equal_separate_runs(toy, tmp_path):
+    """steer_analysis.py:168-183 runs one MCMC per validation point, each against its own pseudo-data: batching them
+    (bi_set_data_sets / bi_log_posterior_sets, one call per half-step for all chains) gives exactly those chains."""
+    import types
+
+    from bayesian_inference_b200 import emulation, log_posterior as lp, mcmc
+
+    d = len(toy.min)
+    F = toy.experimental_results["y"].shape[0]
+    rng = np.random.default_rng(4)
+    pseudo = [{"y": toy.experimental_results["y"] * (1.0 + 0.05 * rng.normal(size=F)),
+               "y_err": toy.experimental_results["y_err"] * rng.uniform(0.8, 1.5, size=F)} for _ in range(3)]
+    cfg = types.SimpleNamespace(
+        analysis_config={"parameterization": {"p": {"names": [f"p{i}" for i in range(d)], "min": list(toy.min), "max": list(toy.max)}}},
+        parameterization="p", analysis_name="toy", config_file="", output_dir=str(tmp_path), mcmc_output_dir=str(tmp_path),
+        n_walkers=16, n_burn_steps=30, n_sampling_steps=40, n_logging_steps=50, sampler_outputfile=None)
+    th = toy.theta[:12]
+    sid = np.arange(12) % 3
+    for mode in ("dense", "structured"):
+        batched = mcmc.run_mcmc_closures(cfg, pseudo, emulation_config=toy.emulation_config,
+                                         emulation_results=toy.emulation_results, seeds=[11, 12, 13], mode=mode)
+        got = lp.device().log_posterior_sets(th, sid, n_div=1.0, mode=mode)      # the handle that holds the three sets
+        for i, p in enumerate(pseudo):
+            single = mcmc.run_mcmc(cfg, closure_index=i, emulation_config=toy.emulation_config,
+                                   emulation_results=toy.emulation_results, experimental_results=p, design_point=None,
+                                   seed=11 + i, write=False, mode=mode)
+            assert np.array_equal(batched[i]["chain"], single["chain"]), (mode, i)
+            assert np.array_equal(batched[i]["log_prob"], single["log_prob"])
+            assert np.array_equal(batched[i]["acceptance_fraction"], single["acceptance_fraction"])
+    # the data-set entry point itself against one handle per data set
+    for c, p in enumerate(pseudo):
+        lp.initialize_pool_variables(toy.min, toy.max, toy.emulation_config, toy.emulation_results, p, None)
+        want = lp.log_posterior_walkers(th[sid == c])
+        assert np.array_equal(got[sid == c], want, equal_nan=True)
+    lp.close()
+    emulation.clear_cache()

@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--walkers", type=int, default=0)
     ap.add_argument("--mode", default="dense")
     ap.add_argument("--block", type=int, default=64)
+    ap.add_argument("--closures", type=int, default=0, help="also run N closure chains batched (SURVEY f3)")
     a = ap.parse_args()
     import torch
 
@@ -36,7 +37,7 @@ def main():
     W, d = spec.n_walkers, spec.d
     x0 = np.random.RandomState(1).uniform(0.3, 0.7, (W, d))
     out = {"workload": spec.name, "walkers": W, "steps": a.steps, "mode": a.mode, "n_obs": img.n_features}
-    with DeviceEmulator(img, max_batch=W) as dev:
+    with DeviceEmulator(img, max_batch=max(W, a.closures * W)) as dev:
         for name, mk in (("host", lambda: StretchEnsemble(W, d, lambda X: dev.log_posterior(X, n_div=1.0, mode=a.mode), seed=3)),
                          ("device", lambda: DeviceStretchEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block))):
             s = mk()
@@ -50,6 +51,24 @@ def main():
             out[name] = {"seconds": dt, "steps_per_s": a.steps / dt, "evals_per_s": s.n_log_prob_rows / dt,
                          "acceptance": float(s.acceptance_fraction.mean())}
             out[name + "_chain_sum"] = float(np.sum(s.get_chain()))
+        if a.closures:
+            from bayesian_inference_b200.ensemble import BatchedClosureEnsemble
+
+            C_ = a.closures
+            rng = np.random.default_rng(9)
+            y, ye = an.experimental_results["y"], an.experimental_results["y_err"]
+            dev.set_data_sets(np.stack([y * (1.0 + 0.03 * rng.normal(size=y.shape)) for _ in range(C_)]), np.stack([ye] * C_))
+            starts = np.stack([np.random.RandomState(100 + c).uniform(0.3, 0.7, (W, d)) for c in range(C_)])
+            BatchedClosureEnsemble(W, d, dev, [np.random.RandomState(c) for c in range(C_)], mode=a.mode, block=a.block).run_mcmc(starts, 5)
+            ens = BatchedClosureEnsemble(W, d, dev, [np.random.RandomState(c) for c in range(C_)], mode=a.mode, block=a.block)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            ens.run_mcmc(starts, a.steps)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            out["closures_batched"] = {"chains": C_, "seconds": dt, "chain_steps_per_s": C_ * a.steps / dt,
+                                       "evals_per_s": ens.n_log_prob_rows / dt,
+                                       "speedup_vs_serial_device_chains": (C_ * a.steps / dt) / out["device"]["steps_per_s"]}
     out["identical_chain"] = out.pop("host_chain_sum") == out.pop("device_chain_sum")
     print(json.dumps(out))
 
