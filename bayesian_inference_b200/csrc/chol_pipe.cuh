@@ -172,14 +172,15 @@ __device__ __forceinline__ void strip_trsm(const double (&a)[2][8], double (&x)[
 //   sD     32 x 33 row-major: in C_jj (lower), out L_jj (lower)
 //   sLjj   [nf][ks][lane] operand-fragment-major L_jj (B operand of the blocked solve), upper part zero
 //   sLinvB [b][kk][lane]: (L_bb)^-1 of the four 8 x 8 diagonal blocks as B fragments
-// returns 0 or the 1-based index of the first non-positive pivot; adds sum(log L_ii) to logdet.
+// returns 0 or the 1-based index of the first non-positive pivot; mypiv = this lane's pivot L_ii^2 (the caller sums
+// 0.5 log of it AFTER it has released the consumers: the logarithm is not on anybody's critical path).
 // aug >= 0: row / column `aug` of this tile is the augmented dY row (see the kernel): its "pivot" is -|L^-1 dY|^2, which is
 // returned in quad and replaced by 1 so that the (identity) padding rows behind it factorise trivially.
-__device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, double* sLinvB, double* sRinv, int lane, double& logdet,
+__device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, double* sLinvB, double* sRinv, int lane, double& mypiv,
                                                   int aug, double& quad) {
     const int g = lane >> 2, t = lane & 3;
     int bad = 0;
-    double mypiv = 1.0;
+    mypiv = 1.0;
 #pragma unroll
     for (int b = 0; b < 4; ++b) {
         double a[8];
@@ -228,7 +229,6 @@ __device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, doub
         __syncwarp();
     }
     if (bad) return bad;
-    logdet += warp_sum(0.5 * log(mypiv));
     // (L_bb)^-1: lane 8b + c computes column c of block b by forward substitution on the identity
     {
         const int b = lane >> 3, c = lane & 7;
@@ -469,7 +469,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             }
         } else if (warp == PIPE_CONSUMERS + 1) {
             // =============================== factor warp ========================================================
-            double logdet = 0.0, quad = 0.0;
+            double lsum = 0.0, quad = 0.0;     // lsum: this lane's share of sum log L_ii
             int first_bad = 0;
             uint32_t gp = gpanel;
 #ifdef PIPE_TIMING
@@ -479,7 +479,8 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
             for (int j = 0; j < nt; ++j, ++gp) {
                 mbar_wait(&bars[BAR_DIAG], gp & 1);
                 TADD(7);
-                const int bad = warp_potrf_blocked(sD, sLinv, sLinvB, sRinv, lane, logdet, j == nt - 1 ? ra : -1, quad);
+                double mypiv;
+                const int bad = warp_potrf_blocked(sD, sLinv, sLinvB, sRinv, lane, mypiv, j == nt - 1 ? ra : -1, quad);
                 TADD(6);
                 if (bad) {
                     if (first_bad == 0) first_bad = j * 32 + bad;
@@ -489,7 +490,9 @@ __global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipePa
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bars[BAR_LINV]);
+                if (!bad) lsum += 0.5 * log(mypiv);
             }
+            const double logdet = warp_sum(lsum);
             if (lane == 0) {
                 sRed[8] = logdet;
                 sRed[9] = quad;
