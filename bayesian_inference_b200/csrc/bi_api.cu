@@ -234,6 +234,15 @@ int launch_chol(bi_handle h, const double* dTheta, const double* dM, const doubl
                     for (int wq = 0; wq < 8; ++wq) v += (double)hb[wq * 8 + c];
                     std::fprintf(stderr, "%s %.1f%%  ", nm[c], 100.0 * v / tot);
                 }
+                {
+                    unsigned long long pz[8];
+                    cudaMemcpyFromSymbol(pz, potrf_dbg, sizeof(pz));
+                    const double np_ = (double)W * h->nt;
+                    std::fprintf(stderr, "| potrf phases (cycles/panel): load %.0f chain %.0f store+trailing %.0f inverse %.0f Ljj %.0f ",
+                                 pz[0] / np_, pz[1] / np_, pz[2] / np_, pz[3] / np_, pz[4] / np_);
+                    unsigned long long zz8[8] = {0};
+                    cudaMemcpyToSymbol(potrf_dbg, zz8, sizeof(zz8));
+                }
                 std::fprintf(stderr, "| wait_full by warp:");
                 for (int wq = 0; wq < 8; ++wq) {
                     double tw = 0;

@@ -176,35 +176,67 @@ __device__ __forceinline__ void strip_trsm(const double (&a)[2][8], double (&x)[
 // 0.5 log of it AFTER it has released the consumers: the logarithm is not on anybody's critical path).
 // aug >= 0: row / column `aug` of this tile is the augmented dY row (see the kernel): its "pivot" is -|L^-1 dY|^2, which is
 // returned in quad and replaced by 1 so that the (identity) padding rows behind it factorise trivially.
+#ifdef PIPE_TIMING
+__device__ unsigned long long potrf_dbg[8];
+#define PT(i) do { long long t1p = clock64(); if (lane == 0) atomicAdd(&potrf_dbg[i], (unsigned long long)(t1p - t0p)); t0p = t1p; } while (0)
+#else
+#define PT(i)
+#endif
 __device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, double* sLinvB, double* sRinv, int lane, double& mypiv,
                                                   int aug, double& quad) {
     const int g = lane >> 2, t = lane & 3;
     int bad = 0;
     mypiv = 1.0;
+#ifdef PIPE_TIMING
+    long long t0p = clock64();
+#endif
 #pragma unroll
     for (int b = 0; b < 4; ++b) {
         double a[8];
 #pragma unroll
         for (int c = 0; c < 8; ++c) a[c] = sD[lane * 33 + 8 * b + c];
+        PT(0);
+        // Two columns at a time.  For the 2 x 2 pivot block [[A, B], [B, C]] the second pivot is det / A with
+        // det = A C - B^2, so 1 / sqrt(A) and 1 / sqrt(det) are independent and the chain carries ONE reciprocal square
+        // root per pair of columns instead of two (same cancellation as C - B^2 / A; the chain is what the consumers wait for).
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-            double p = shfl_d(a[c], 8 * b + c);
-            if (8 * b + c == aug) {
-                quad = -p;
-                p = 1.0;
+        for (int c = 0; c < 8; c += 2) {
+            const int k0 = 8 * b + c, k1 = k0 + 1;
+            double A = shfl_d(a[c], k0);
+            const double B = shfl_d(a[c], k1);
+            const double Cc = shfl_d(a[c + 1], k1);
+            if (k0 == aug) {                    // the augmented dY row: its would-be pivot is -|L^-1 dY|^2
+                quad = -A;
+                A = 1.0;
                 if (lane == aug) a[c] = 1.0;
             }
-            if (!(p > 0.0) && bad == 0) bad = 8 * b + c + 1;
-            if (lane == 8 * b + c) mypiv = p;
-            const double rinv = rsqrt(p);
-            a[c] *= rinv;                       // rows below the pivot: L[r][8b+c]; the pivot row: sqrt(p)
-            if (lane == 8 * b + c) sRinv[8 * b + c] = rinv;
+            const double det = fma(A, Cc, -(B * B));
+            double r1 = rsqrt(A);
+            double rd = rsqrt(det);
+            if (!(A > 0.0) && bad == 0) bad = k0 + 1;
+            double p2 = det * (r1 * r1);        // second pivot
+            double r2 = rd * (A * r1);          // 1 / sqrt(det / A)
+            if (k1 == aug) {
+                quad = -p2;
+                p2 = 1.0;
+                r2 = 1.0;
+            }
+            if (!(p2 > 0.0) && bad == 0) bad = k1 + 1;
+            if (lane == k0) mypiv = A;
+            if (lane == k1) mypiv = p2;
+            const double l21 = B * r1;
+            a[c] *= r1;                         // L[r][k0]; the pivot row: sqrt(A)
+            a[c + 1] = fma(-a[c], l21, a[c + 1]) * r2;
+            if (k1 == aug && lane == aug) a[c + 1] = 1.0;
+            if (lane == k0) sRinv[k0] = r1;
+            if (lane == k1) sRinv[k1] = r2;
 #pragma unroll
-            for (int c2 = c + 1; c2 < 8; ++c2) {
-                const double l = shfl_d(a[c], 8 * b + c2);
-                a[c2] = fma(-a[c], l, a[c2]);
+            for (int c2 = c + 2; c2 < 8; ++c2) {
+                const double la = shfl_d(a[c], 8 * b + c2), lb = shfl_d(a[c + 1], 8 * b + c2);
+                a[c2] = fma(-a[c + 1], lb, fma(-a[c], la, a[c2]));
             }
         }
+        PT(1);
 #pragma unroll
         for (int c = 0; c < 8; ++c)
             if (lane >= 8 * b + c) sD[lane * 33 + 8 * b + c] = a[c];
@@ -227,6 +259,7 @@ __device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, doub
             }
         }
         __syncwarp();
+        PT(2);
     }
     if (bad) return bad;
     // (L_bb)^-1: lane 8b + c computes column c of block b by forward substitution on the identity
@@ -243,6 +276,7 @@ __device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, doub
 #pragma unroll
         for (int n = 0; n < 8; ++n) sLinvB[(b * 2 + (c >> 2)) * 32 + n * 4 + (c & 3)] = x[n];
     }
+    PT(3);
     // L_jj as B operand
 #pragma unroll 4
     for (int idx = lane; idx < TILE_ELEMS; idx += 32) {
@@ -250,6 +284,7 @@ __device__ __forceinline__ int warp_potrf_blocked(double* sD, double* sLjj, doub
         const int n = 8 * nf + g, k = 4 * ks + t;
         sLjj[idx] = (k <= n) ? sD[n * 33 + k] : 0.0;
     }
+    PT(4);
     return 0;
 }
 
