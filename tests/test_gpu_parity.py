@@ -188,6 +188,26 @@ def test_full_size_torch_device_path_matches_host_path(c3a):
     assert np.array_equal(out.cpu().numpy(), dev.log_posterior(a.theta, n_div=1.0))
 
 
+def test_largest_configuration_c5_modes_agree_and_match_oracle():
+    """BASELINE configs[4] shapes (n_design=500, n_pc=50, n_obs=2000): oracle on 3 rows, and dense == structured ==
+    Woodbury on 96 walkers (the factor scratch of one CTA is 16 MB here, the operand ring sweeps 62 chunks)."""
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    a = synthetic.generate("C5A", n_walkers=96, oob_fraction=0.05)
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max,
+                     experimental_results=a.experimental_results)
+    with DeviceEmulator(img, max_batch=96) as dev:
+        d = dev.log_posterior(a.theta, n_div=1.0, mode="dense")
+        fin = np.isfinite(d)
+        assert fin.sum() >= 80
+        for mode in ("structured", "woodbury"):
+            s_ = dev.log_posterior(a.theta, n_div=1.0, mode=mode)
+            assert np.array_equal(np.isneginf(d), np.isneginf(s_)) and rel_err(s_[fin], d[fin]) < TOL_LOGP
+        idx = np.flatnonzero(fin)[:3]
+        want = cf.log_posterior(img.to_flat(), a.theta[idx], n_div=1.0)
+        assert rel_err(d[idx], want) < TOL_LOGP
+
+
 # ---- edge cases ---------------------------------------------------------------------------------------------------
 def test_edge_cases_empty_single_all_outside():
     z, ref = load_golden("toy")
