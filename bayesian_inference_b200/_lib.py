@@ -25,6 +25,8 @@ EXPORTS = [
     "bi_predict_group", "bi_predict_group_host", "bi_predict", "bi_predict_host",
     "bi_log_posterior", "bi_log_posterior_host", "bi_loglikelihood_host",
     "bi_stretch_propose", "bi_stretch_accept", "bi_set_data_sets", "bi_log_posterior_sets",
+    "bi_trainer_create", "bi_trainer_lml", "bi_trainer_lml_host", "bi_trainer_factor", "bi_trainer_factor_host",
+    "bi_trainer_destroy", "bi_trainer_last_error", "bi_trainer_launches",
 ]
 
 MODE = {"dense": 0, "structured": 1, "woodbury": 2}
@@ -131,7 +133,19 @@ def load() -> C.CDLL:
     lib.bi_stretch_accept.argtypes = [h, dp, dp, dp, dp, dp, dp, dp, i64, dp, dp, C.c_void_p]
     lib.bi_set_data_sets.argtypes = [h, C.c_int32, dp, dp]
     lib.bi_log_posterior_sets.argtypes = [h, dp, dp, i64, C.c_double, C.c_int, dp, dp, C.c_void_p]
-    for name in EXPORTS[8:]:
+    i32 = C.c_int32
+    lib.bi_trainer_create.argtypes = [dp, i32, i32, dp, i32, i32, i32, i32, C.c_double, i32, C.POINTER(C.c_void_p)]
+    lib.bi_trainer_lml.argtypes = [h, dp, dp, i64, dp, dp, C.c_void_p]
+    lib.bi_trainer_lml_host.argtypes = [h, dp, dp, i64, dp, dp]
+    lib.bi_trainer_factor.argtypes = [h, dp, dp, i64, dp, dp, dp, C.c_void_p]
+    lib.bi_trainer_factor_host.argtypes = [h, dp, dp, i64, dp, dp, dp]
+    lib.bi_trainer_destroy.argtypes = [h]
+    lib.bi_trainer_destroy.restype = None
+    lib.bi_trainer_last_error.argtypes = [h]
+    lib.bi_trainer_last_error.restype = C.c_char_p
+    lib.bi_trainer_launches.argtypes = [h]
+    lib.bi_trainer_launches.restype = C.c_int64
+    for name in EXPORTS[8:28]:
         getattr(lib, name).restype = C.c_int
     if lib.bi_abi_version() != 1:
         raise BackendUnavailable(f"ABI version mismatch: library {lib.bi_abi_version()}, package 1")

@@ -17,6 +17,7 @@
 #include "cov_assemble.cuh"
 #include "ensemble.cuh"
 #include "gp_predict.cuh"
+#include "gp_train.cuh"
 #include "setup_kernels.cuh"
 #include "woodbury.cuh"
 
@@ -1112,6 +1113,148 @@ int bi_log_posterior_sets(bi_handle h, const double* theta, const int32_t* set_i
         if (rc) return rc;
     }
     return 0;
+}
+
+// ---- emulator training objective: batched log-marginal-likelihood + gradient ---------------------------
+struct bi_trainer_s {
+    int device = 0, N = 0, d = 0, n_y = 0, kind = 0, has_const = 0, has_white = 0, nh = 0, sms = 0, nwarps = 0, occ = 1;
+    double alpha = 0.0;
+    double *dX = nullptr, *dY = nullptr, *dScratch = nullptr;
+    size_t smem = 0, slot = 0;
+    int nslots = 0;
+    long long launches = 0;
+    std::string err;
+};
+
+static int tfail(bi_trainer t, int code, const std::string& msg) {
+    if (t) t->err = msg;
+    return code;
+}
+#define TCK(call)                                                                      \
+    do {                                                                               \
+        cudaError_t e_ = (call);                                                       \
+        if (e_ != cudaSuccess) return tfail(t, (int)e_, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, int32_t n_y, int32_t kind, int32_t has_const,
+                      int32_t has_white, double alpha, int32_t device, bi_trainer* out) {
+    if (!out) return BI_E_ARG;
+    *out = nullptr;
+    if (!X || !Y || N < 1 || N > 32 * TRAIN_MAX_NT || d < 1 || d > TRAIN_MAX_D || n_y < 1 || kind < 0 || kind > 3 || !(alpha >= 0.0))
+        return BI_E_ARG;
+    bi_trainer t = new bi_trainer_s();
+    t->device = device; t->N = N; t->d = d; t->n_y = n_y; t->kind = kind;
+    t->has_const = has_const ? 1 : 0; t->has_white = has_white ? 1 : 0; t->alpha = alpha;
+    t->nh = d + t->has_const + t->has_white;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&t->sms, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dX, sizeof(double) * N * d);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dY, sizeof(double) * (size_t)n_y * N);
+    if (e == cudaSuccess) e = cudaMemcpy(t->dX, X, sizeof(double) * N * d, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(t->dY, Y, sizeof(double) * (size_t)n_y * N, cudaMemcpyHostToDevice);
+    const int nt = (N + 31) / 32;
+    t->nwarps = std::max(2, std::min(nt, 16));
+    if (const char* s = getenv("BI_TRAIN_WARPS")) t->nwarps = std::max(1, std::min(16, atoi(s)));
+    if (const char* s = getenv("BI_TRAIN_OCC")) t->occ = std::max(1, std::min(8, atoi(s)));
+    t->smem = lml_smem_bytes(N, d, t->nwarps);
+    t->slot = lml_scratch_doubles(N);
+    t->nslots = t->sms * t->occ;
+    if (e == cudaSuccess && t->smem > 48 * 1024)
+        e = cudaFuncSetAttribute(gp_lml_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dScratch, sizeof(double) * t->slot * t->nslots);
+    if (e != cudaSuccess) {
+        const int rc = (int)e;
+        cudaFree(t->dX); cudaFree(t->dY); cudaFree(t->dScratch);
+        delete t;
+        return rc;
+    }
+    *out = t;
+    return 0;
+}
+
+void bi_trainer_destroy(bi_trainer t) {
+    if (!t) return;
+    cudaSetDevice(t->device);
+    cudaFree(t->dX); cudaFree(t->dY); cudaFree(t->dScratch);
+    delete t;
+}
+
+const char* bi_trainer_last_error(bi_trainer t) { return t ? t->err.c_str() : "null trainer"; }
+int64_t bi_trainer_launches(bi_trainer t) { return t ? t->launches : 0; }
+
+static int trainer_launch(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml, double* grad,
+                          double* L_out, double* alpha_out, cudaStream_t s) {
+    LmlParams P;
+    P.X = t->dX; P.Y = t->dY; P.y_index = y_index; P.theta = theta; P.B = B;
+    P.N = t->N; P.d = t->d; P.nh = t->nh; P.kind = t->kind; P.has_const = t->has_const; P.has_white = t->has_white;
+    P.alpha = t->alpha; P.scratch = t->dScratch; P.scratch_stride = (long long)t->slot;
+    P.lml = lml; P.grad = grad; P.L_out = L_out; P.alpha_out = alpha_out;
+    const unsigned grid = (unsigned)std::min<long long>(B, t->nslots);
+    gp_lml_kernel<<<grid, t->nwarps * 32, t->smem, s>>>(P);
+    t->launches++;
+    TCK(cudaGetLastError());
+    return 0;
+}
+
+int bi_trainer_lml(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml_out, double* grad_out,
+                   void* stream) {
+    if (!t || !theta || !lml_out || !grad_out || B < 0) return tfail(t, BI_E_ARG, "bad argument");
+    if (!y_index && B > t->n_y) return tfail(t, BI_E_ARG, "y_index required when B exceeds the number of target rows");
+    if (B == 0) return 0;
+    TCK(cudaSetDevice(t->device));
+    return trainer_launch(t, theta, y_index, B, lml_out, grad_out, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+int bi_trainer_factor(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml_out, double* L_out,
+                      double* alpha_out, void* stream) {
+    if (!t || !theta || !lml_out || !L_out || !alpha_out || B < 0) return tfail(t, BI_E_ARG, "bad argument");
+    if (!y_index && B > t->n_y) return tfail(t, BI_E_ARG, "y_index required when B exceeds the number of target rows");
+    if (B == 0) return 0;
+    TCK(cudaSetDevice(t->device));
+    return trainer_launch(t, theta, y_index, B, lml_out, nullptr, L_out, alpha_out, (cudaStream_t)stream);
+}
+
+static int trainer_host(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml_out, double* grad_out,
+                        double* L_out, double* alpha_out) {
+    if (!t || !theta || !lml_out || B < 0) return tfail(t, BI_E_ARG, "bad argument");
+    if (!y_index && B > t->n_y) return tfail(t, BI_E_ARG, "y_index required when B exceeds the number of target rows");
+    if (y_index)
+        for (int64_t b = 0; b < B; ++b)
+            if (y_index[b] < 0 || y_index[b] >= t->n_y) return tfail(t, BI_E_ARG, "y_index out of range");
+    if (B == 0) return 0;
+    TCK(cudaSetDevice(t->device));
+    const size_t NN = (size_t)t->N * t->N;
+    double *dTh = nullptr, *dLml = nullptr, *dGrad = nullptr, *dL = nullptr, *dAl = nullptr;
+    int32_t* dIdx = nullptr;
+    int rc = 0;
+    cudaError_t e = cudaMalloc(&dTh, sizeof(double) * B * t->nh);
+    if (e == cudaSuccess) e = cudaMalloc(&dLml, sizeof(double) * B);
+    if (e == cudaSuccess && grad_out) e = cudaMalloc(&dGrad, sizeof(double) * B * t->nh);
+    if (e == cudaSuccess && L_out) e = cudaMalloc(&dL, sizeof(double) * B * NN);
+    if (e == cudaSuccess && L_out) e = cudaMalloc(&dAl, sizeof(double) * B * t->N);
+    if (e == cudaSuccess && y_index) e = cudaMalloc(&dIdx, sizeof(int32_t) * B);
+    if (e == cudaSuccess) e = cudaMemcpy(dTh, theta, sizeof(double) * B * t->nh, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && y_index) e = cudaMemcpy(dIdx, y_index, sizeof(int32_t) * B, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) rc = trainer_launch(t, dTh, dIdx, B, dLml, dGrad, dL, dAl, nullptr);
+    if (e == cudaSuccess && rc == 0) e = cudaDeviceSynchronize();
+    if (e == cudaSuccess && rc == 0) e = cudaMemcpy(lml_out, dLml, sizeof(double) * B, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && rc == 0 && grad_out) e = cudaMemcpy(grad_out, dGrad, sizeof(double) * B * t->nh, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && rc == 0 && L_out) e = cudaMemcpy(L_out, dL, sizeof(double) * B * NN, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && rc == 0 && L_out) e = cudaMemcpy(alpha_out, dAl, sizeof(double) * B * t->N, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) rc = tfail(t, (int)e, std::string("bi_trainer host call: ") + cudaGetErrorString(e));
+    cudaFree(dTh); cudaFree(dLml); cudaFree(dGrad); cudaFree(dL); cudaFree(dAl); cudaFree(dIdx);
+    return rc;
+}
+
+int bi_trainer_lml_host(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml_out, double* grad_out) {
+    if (!grad_out) return tfail(t, BI_E_ARG, "bad argument");
+    return trainer_host(t, theta, y_index, B, lml_out, grad_out, nullptr, nullptr);
+}
+
+int bi_trainer_factor_host(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml_out, double* L_out,
+                           double* alpha_out) {
+    if (!L_out || !alpha_out) return tfail(t, BI_E_ARG, "bad argument");
+    return trainer_host(t, theta, y_index, B, lml_out, nullptr, L_out, alpha_out);
 }
 
 }  // extern "C"

@@ -14,6 +14,7 @@
  *   log_posterior.log_posterior              log_posterior.py:42   bi_log_posterior[_host]
  *   log_posterior._loglikelihood             log_posterior.py:104  bi_loglikelihood_host
  *   emcee stretch move driven by mcmc.run_mcmc  mcmc.py:83-107     bi_stretch_propose / bi_stretch_accept
+ *   GaussianProcessRegressor.fit objective   emulation.py:169-172  bi_trainer_lml / bi_trainer_factor
  *
  * Conventions
  *   - every matrix is row-major float64; every index is 0-based;
@@ -178,6 +179,37 @@ int bi_stretch_accept(bi_handle h, double* coords, double* logp, const int32_t* 
 int bi_set_data_sets(bi_handle h, int32_t n_sets, const double* y, const double* y_err);
 int bi_log_posterior_sets(bi_handle h, const double* theta, const int32_t* set_id, int64_t W, double n_div, int mode,
                           double* logp_out, int32_t* info_out, void* stream);
+
+/* ---- emulator training objective (emulation.py:128-172 -> sklearn GaussianProcessRegressor.fit, _gpr.py:296-366) -------
+ * The reference fits one GP per principal component with n_restarts optimiser starts; each objective evaluation is
+ * log_marginal_likelihood(theta, eval_gradient=True) (_gpr.py:541-639).  A trainer holds the design X (N, d) and the
+ * targets Y (n_y, N) (rows = principal-component scores, Y_pca_truncated.T) on the device and evaluates any number of
+ * hyper-parameter vectors in one launch.  kind = BI_KERNEL_* (Matern 1/2, 3/2, 5/2, RBF); has_const / has_white say
+ * whether the kernel is "+ ConstantKernel" / "+ WhiteKernel"; alpha is the jitter GaussianProcessRegressor(alpha=...)
+ * adds to the diagonal.  theta (B, n_hyper) is scikit-learn's kernel.theta: log length scales [d], then
+ * log constant_value, then log noise_level (those that exist).  y_index (B) names the row of Y per vector
+ * (NULL: vector b uses row b, B <= n_y).
+ *
+ * bi_trainer_lml   : lml_out (B), grad_out (B, n_hyper).  A matrix that is not positive definite gives -inf and a zero
+ *                    gradient, as scikit-learn does (_gpr.py:586-589).
+ * bi_trainer_factor: what fit() keeps for predict (_gpr.py:335-366): L_out (B, N, N) = chol(K + alpha I) lower,
+ *                    alpha_out (B, N) = K^-1 y, lml_out (B).
+ * The plain calls take DEVICE pointers and enqueue on `stream`; the _host calls take HOST pointers and synchronise.
+ * N <= 992, d <= 16. */
+typedef struct bi_trainer_s* bi_trainer;
+int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, int32_t n_y, int32_t kind,
+                      int32_t has_const, int32_t has_white, double alpha, int32_t device, bi_trainer* out);
+void bi_trainer_destroy(bi_trainer t);
+const char* bi_trainer_last_error(bi_trainer t);
+int64_t bi_trainer_launches(bi_trainer t);
+int bi_trainer_lml(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml_out,
+                   double* grad_out, void* stream);
+int bi_trainer_lml_host(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml_out,
+                        double* grad_out);
+int bi_trainer_factor(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml_out,
+                      double* L_out, double* alpha_out, void* stream);
+int bi_trainer_factor_host(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml_out,
+                           double* L_out, double* alpha_out);
 
 #ifdef __cplusplus
 }
