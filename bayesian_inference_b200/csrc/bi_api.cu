@@ -1119,9 +1119,10 @@ int bi_log_posterior_sets(bi_handle h, const double* theta, const int32_t* set_i
 struct bi_trainer_s {
     int device = 0, N = 0, d = 0, n_y = 0, kind = 0, has_const = 0, has_white = 0, nh = 0, sms = 0, nwarps = 0, occ = 1;
     double alpha = 0.0;
-    double *dX = nullptr, *dY = nullptr, *dScratch = nullptr;
-    size_t smem = 0, slot = 0;
-    int nslots = 0;
+    double *dX = nullptr, *dY = nullptr, *dScratch = nullptr, *dKt = nullptr, *dAb = nullptr;
+    size_t smem_factor = 0, smem_grad = 0, slot = 0, tiles = 0;
+    long long cap = 0, chunk_max = 0;      // problems the K / alpha buffers hold now; upper limit per launch group
+    int nslots = 0, ntri = 0, Np = 0;
     long long launches = 0;
     std::string err;
 };
@@ -1135,6 +1136,30 @@ static int tfail(bi_trainer t, int code, const std::string& msg) {
         cudaError_t e_ = (call);                                                       \
         if (e_ != cudaSuccess) return tfail(t, (int)e_, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
+
+}  // extern "C"
+template <int KIND>
+static cudaError_t trainer_attrs(bi_trainer t) {
+    cudaError_t e = cudaSuccess;
+    if (t->smem_grad > 48 * 1024) {
+        e = cudaFuncSetAttribute(gp_grad_kernel<KIND, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_grad);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(gp_grad_kernel<KIND, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_grad);
+    }
+    return e;
+}
+template <int KIND>
+static void trainer_kernels(bi_trainer t, const LmlParams& P, bool with_grad, cudaStream_t s) {
+    gp_kbuild_kernel<KIND><<<dim3((unsigned)t->ntri, (unsigned)P.B), 256, 0, s>>>(P);
+    const unsigned grid = (unsigned)std::min<long long>(P.B, t->nslots);
+    gp_factor_kernel<<<grid, t->nwarps * 32, t->smem_factor, s>>>(P);
+    if (with_grad) {
+        if (t->d <= 8) gp_grad_kernel<KIND, 8><<<(unsigned)P.B, 512, t->smem_grad, s>>>(P);
+        else gp_grad_kernel<KIND, 16><<<(unsigned)P.B, 512, t->smem_grad, s>>>(P);
+    }
+    t->launches += with_grad ? 3 : 2;
+}
+extern "C" {
 
 int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, int32_t n_y, int32_t kind, int32_t has_const,
                       int32_t has_white, double alpha, int32_t device, bi_trainer* out) {
@@ -1153,14 +1178,22 @@ int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, in
     if (e == cudaSuccess) e = cudaMemcpy(t->dX, X, sizeof(double) * N * d, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(t->dY, Y, sizeof(double) * (size_t)n_y * N, cudaMemcpyHostToDevice);
     const int nt = (N + 31) / 32;
-    t->nwarps = std::max(2, std::min(nt, 16));
-    if (const char* s = getenv("BI_TRAIN_WARPS")) t->nwarps = std::max(1, std::min(16, atoi(s)));
+    t->ntri = nt * (nt + 1) / 2;
+    t->Np = nt * 32;
+    t->nwarps = std::max(2, std::min(nt, 16));          // one warp per unit of a panel (nt units)
+    t->occ = std::max(1, 16 / t->nwarps);               // 512 threads per SM at 128 registers
+    if (const char* s = getenv("BI_TRAIN_WARPS")) t->nwarps = std::max(2, std::min(16, atoi(s)));
     if (const char* s = getenv("BI_TRAIN_OCC")) t->occ = std::max(1, std::min(8, atoi(s)));
-    t->smem = lml_smem_bytes(N, d, t->nwarps);
-    t->slot = lml_scratch_doubles(N);
+    t->smem_factor = lml_factor_smem_bytes(N, t->nwarps);
+    t->smem_grad = lml_grad_smem_bytes(N, d);
+    t->tiles = lml_tiles_doubles(N);
+    t->slot = t->tiles;                                  // M = L^-T has as many tiles as the lower triangle
     t->nslots = t->sms * t->occ;
-    if (e == cudaSuccess && t->smem > 48 * 1024)
-        e = cudaFuncSetAttribute(gp_lml_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem);
+    // the K / K^-1 tiles of a launch group live in HBM: at most ~4 GB of them at a time
+    t->chunk_max = std::max<long long>(t->nslots, (long long)((4ull << 30) / (t->tiles * sizeof(double))));
+    if (e == cudaSuccess && t->smem_factor > 48 * 1024)
+        e = cudaFuncSetAttribute(gp_factor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_factor);
+    if (e == cudaSuccess) e = kind == 0 ? trainer_attrs<0>(t) : kind == 1 ? trainer_attrs<1>(t) : kind == 2 ? trainer_attrs<2>(t) : trainer_attrs<3>(t);
     if (e == cudaSuccess) e = cudaMalloc(&t->dScratch, sizeof(double) * t->slot * t->nslots);
     if (e != cudaSuccess) {
         const int rc = (int)e;
@@ -1175,7 +1208,7 @@ int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, in
 void bi_trainer_destroy(bi_trainer t) {
     if (!t) return;
     cudaSetDevice(t->device);
-    cudaFree(t->dX); cudaFree(t->dY); cudaFree(t->dScratch);
+    cudaFree(t->dX); cudaFree(t->dY); cudaFree(t->dScratch); cudaFree(t->dKt); cudaFree(t->dAb);
     delete t;
 }
 
@@ -1184,15 +1217,49 @@ int64_t bi_trainer_launches(bi_trainer t) { return t ? t->launches : 0; }
 
 static int trainer_launch(bi_trainer t, const double* theta, const int32_t* y_index, int64_t B, double* lml, double* grad,
                           double* L_out, double* alpha_out, cudaStream_t s) {
-    LmlParams P;
-    P.X = t->dX; P.Y = t->dY; P.y_index = y_index; P.theta = theta; P.B = B;
-    P.N = t->N; P.d = t->d; P.nh = t->nh; P.kind = t->kind; P.has_const = t->has_const; P.has_white = t->has_white;
-    P.alpha = t->alpha; P.scratch = t->dScratch; P.scratch_stride = (long long)t->slot;
-    P.lml = lml; P.grad = grad; P.L_out = L_out; P.alpha_out = alpha_out;
-    const unsigned grid = (unsigned)std::min<long long>(B, t->nslots);
-    gp_lml_kernel<<<grid, t->nwarps * 32, t->smem, s>>>(P);
-    t->launches++;
-    TCK(cudaGetLastError());
+    const long long need = std::min<long long>(B, t->chunk_max);
+    if (need > t->cap) {                               // grow the K / alpha buffers (stream-ordered free of the old ones)
+        TCK(cudaStreamSynchronize(s));
+        cudaFree(t->dKt); cudaFree(t->dAb);
+        t->dKt = t->dAb = nullptr;
+        t->cap = 0;
+        TCK(cudaMalloc(&t->dKt, sizeof(double) * t->tiles * need));
+        TCK(cudaMalloc(&t->dAb, sizeof(double) * (size_t)t->Np * need));
+        t->cap = need;
+    }
+    for (int64_t b0 = 0; b0 < B; b0 += t->cap) {
+        LmlParams P;
+        P.B = std::min<long long>(t->cap, B - b0);
+        P.X = t->dX; P.Y = t->dY; P.y_index = y_index ? y_index + b0 : nullptr; P.theta = theta + b0 * t->nh;
+        if (!y_index) P.Y = t->dY + b0 * t->N;         // problem b uses row b
+        P.N = t->N; P.d = t->d; P.nh = t->nh; P.has_const = t->has_const; P.has_white = t->has_white;
+        P.alpha = t->alpha; P.Kt = t->dKt; P.Ab = t->dAb; P.scratch = t->dScratch; P.scratch_stride = (long long)t->slot;
+        P.lml = lml + b0; P.grad = grad ? grad + b0 * t->nh : nullptr;
+        P.L_out = L_out ? L_out + (size_t)b0 * t->N * t->N : nullptr;
+        P.alpha_out = alpha_out ? alpha_out + (size_t)b0 * t->N : nullptr;
+#ifdef TRAIN_TIMING
+        { unsigned long long z[12] = {0}; cudaMemcpyToSymbolAsync(train_dbg, z, sizeof(z), 0, cudaMemcpyHostToDevice, s); }
+#endif
+        const bool wg = grad != nullptr;
+        switch (t->kind) {
+            case 0: trainer_kernels<0>(t, P, wg, s); break;
+            case 1: trainer_kernels<1>(t, P, wg, s); break;
+            case 2: trainer_kernels<2>(t, P, wg, s); break;
+            default: trainer_kernels<3>(t, P, wg, s); break;
+        }
+#ifdef TRAIN_TIMING
+        {
+            unsigned long long z[12];
+            cudaMemcpyFromSymbolAsync(z, train_dbg, sizeof(z), 0, cudaMemcpyDeviceToHost, s);
+            cudaStreamSynchronize(s);
+            const double nb = (double)P.B;
+            std::fprintf(stderr, "[train timing] cycles per problem (thread 0): load %.0f  diag update %.0f  potrf+inv %.0f  wait updates %.0f  "
+                         "solves %.0f  z %.0f  alpha %.0f  Kinv %.0f\n", z[0] / nb, z[1] / nb, z[2] / nb, z[3] / nb,
+                         z[4] / nb, z[5] / nb, z[6] / nb, z[7] / nb);
+        }
+#endif
+        TCK(cudaGetLastError());
+    }
     return 0;
 }
 

@@ -5,8 +5,13 @@
 // (emulation.py:128-172); every objective evaluation is scikit-learn's log_marginal_likelihood(theta, eval_gradient=True)
 // (_gpr.py:541-639): K = k(X, X; theta) + alpha I, L = chol(K), a = K^-1 y,
 //     lml  = -1/2 y.a - sum log L_ii - N/2 log 2 pi,        grad_m = 1/2 tr((a a^T - K^-1) dK/dtheta_m).
-// All restarts of all principal components are independent, so they are evaluated as one batch: one CTA per
-// hyper-parameter vector, persistent over the batch, its N x N working set in an L2-resident scratch slot.
+// All restarts of all principal components are independent, so they are evaluated as one batch, in three launches:
+//   gp_kbuild_kernel  element-wise: K + alpha I of every problem as 32 x 32 tiles (lower triangle)       [FP64 ALU]
+//   gp_factor_kernel  one CTA per problem, persistent: Cholesky, L^-T, K^-1, a, the LML                   [FP64 tensor]
+//   gp_grad_kernel    element-wise: the trace contraction with dK/dtheta recomputed on the fly            [FP64 ALU]
+// The element-wise phases are separate launches on purpose: inside the factorisation kernel their dependent sqrt / exp
+// chains queued behind the other warps' DMMAs on the shared FP64 pipe (~100 cycles per dependent instruction, measured)
+// and took a third of its time; at full occupancy on their own they are throughput bound.
 //
 // One code path does the factorisation, the inverse factor and K^-1: a left-looking blocked Cholesky of the augmented
 // matrix [[K, I], [I, 0]] with 32 x 32 tiles.  Its lower-left block is M = L^-T (upper block triangular, so its tiles
@@ -21,6 +26,7 @@
 #include <stdint.h>
 
 #include "common.cuh"
+#include "gp_predict.cuh"      // exp_neg / sqrt_pos: branch-free exp(-x), sqrt(x) (<= 2 ulp)
 
 namespace bi {
 
@@ -34,26 +40,39 @@ struct LmlParams {
     const int* y_index;     // (B) row of Y per problem, or nullptr: problem b uses row b
     const double* theta;    // (B, nh) log hyper-parameters in scikit-learn order: log ell[0..d-1], [log c], [log eta]
     long long B;
-    int N, d, nh, kind, has_const, has_white;
+    int N, d, nh, has_const, has_white;
     double alpha;
-    double* scratch;        // gridDim.x slots of scratch_stride doubles
+    double* Kt;             // (B, ntri, 1024) lower tiles: K + alpha I in, L during the factorisation, K^-1 out
+    double* Ab;             // (B, Np) K^-1 y
+    double* scratch;        // gridDim.x slots of scratch_stride doubles: the tiles of M = L^-T
     long long scratch_stride;
     double* lml;            // (B)
-    double* grad;           // (B, nh); unused when L_out is set
+    double* grad;           // (B, nh); not written when L_out is set
     double* L_out;          // optional (B, N, N): chol(K + alpha I), lower, zeros above  (scikit-learn's L_)
     double* alpha_out;      // optional (B, N): K^-1 y                                      (scikit-learn's alpha_)
 };
 
+#ifdef TRAIN_TIMING
+__device__ unsigned long long train_dbg[12];   // developer timing: cycles of thread 0 per phase, summed over problems
+#define TR_T(i) do { if (threadIdx.x == 0) { long long t1_ = clock64(); atomicAdd(&train_dbg[i], (unsigned long long)(t1_ - t0_)); t0_ = t1_; } } while (0)
+#else
+#define TR_T(i)
+#endif
+
 __host__ __device__ __forceinline__ int tri_idx(int i, int j) { return i * (i + 1) / 2 + j; }
 
-__host__ inline size_t lml_scratch_doubles(int N) {
+__host__ inline size_t lml_tiles_doubles(int N) {        // per problem: lower tiles of K / L / K^-1
     const int nt = (N + 31) / 32;
-    return (size_t)nt * (nt + 1) * 1024;      // lower tiles of L (later K^-1) + tiles of M = L^-T
+    return (size_t)nt * (nt + 1) / 2 * 1024;
 }
-__host__ inline size_t lml_smem_bytes(int N, int d, int nwarps) {
+__host__ inline size_t lml_factor_smem_bytes(int N, int nwarps) {
     const int nt = (N + 31) / 32, Np = nt * 32;
-    size_t dbl = (size_t)((N * d + 1) & ~1) + 3 * (size_t)Np + 32 * TRAIN_LDY + (size_t)nwarps * (TRAIN_MAX_D + 4) + 2 * TRAIN_MAX_D + 8;
+    size_t dbl = 3 * (size_t)Np + 32 * TRAIN_LDY + 32 * 33 + (size_t)nwarps + 8;
     return dbl * 8 + (size_t)nt * (nt + 1) / 2 * 2 * sizeof(int) + 16;
+}
+__host__ inline size_t lml_grad_smem_bytes(int N, int d) {
+    const int nt = (N + 31) / 32, Np = nt * 32;
+    return ((size_t)((N * d + 1) & ~1) + Np + 32 * (TRAIN_MAX_D + 2) + TRAIN_MAX_D + 4) * 8 + (size_t)nt * (nt + 1) / 2 * 2 * sizeof(int) + 16;
 }
 
 // acc (+/-)= A * B^T for 32 x 32 row-major tiles (A: leading dimension 32; B: leading dimension LDB).
@@ -112,93 +131,160 @@ __device__ __forceinline__ void acc_store(const double (&acc)[4][4][2], double* 
             *reinterpret_cast<double2*>(p + mf * 256 + nf * 8) = make_double2(acc[mf][nf][0], acc[mf][nf][1]);
 }
 
-// Warp 0: factorise the 32 x 32 diagonal tile T in place (lower, zeros above), write Y = L_jj^-1 row-major into sY
-// (stride TRAIN_LDY) and M_jj = Y^T into Mjj.  Returns sum log L_kk over the tile's rows; ok = 0 on a non-positive pivot.
-__device__ __forceinline__ double warp_potrf_inv(double* T, double* sYinv, double* Mjj, int lane, int& ok) {
-    double a[32];
+// sqrt(s) and 1/sqrt(s) together (s > 0): MUFU.RSQ64H seed (2^-20) + two coupled Goldschmidt steps (-> 2^-80, i.e.
+// rounding-limited, <= 2 ulp).  No final correction: every dependent FP64 instruction of the factorisation's column
+// chain costs ~100 cycles while the other warps keep the FP64 pipe busy with DMMAs.
+__device__ __forceinline__ void sqrt_rsqrt(double s, double& root, double& rinv) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(s));
+    double g = s * y, h = 0.5 * y;
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+        const double r = fma(-g, h, 0.5);
+        g = fma(g, r, g);
+        h = fma(h, r, h);
+    }
+    root = g;
+    rinv = h + h;
+}
+
+// Warp 0: factorise the 32 x 32 diagonal tile T in place (lower, zeros above), write Y = L_jj^-1 row-major into sYinv
+// (stride TRAIN_LDY) and M_jj = Y^T into Mjj.  sL: 32 x 33 scratch for L_jj.  Returns sum log L_kk over the tile's rows;
+// ok = 0 on a non-positive pivot.
+__device__ __noinline__ double warp_potrf_inv(double* T, double* sYinv, double* sL, double* Mjj, int lane, int& ok) {
+    double mypiv = 1.0, myrinv = 1.0;
     {
+        double a[32];      // lane = row
         const double4* row = reinterpret_cast<const double4*>(T + lane * 32);
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
             const double4 v = row[q];
             a[4 * q] = v.x; a[4 * q + 1] = v.y; a[4 * q + 2] = v.z; a[4 * q + 3] = v.w;
         }
-    }
-    double mypiv = 1.0, myrinv = 1.0;
 #pragma unroll
-    for (int k = 0; k < 32; ++k) {
-        const double piv = shfl_d(a[k], k);
-        if (!(piv > 0.0)) ok = 0;
-        const double lkk = sqrt(piv);
-        const double rinv = 1.0 / lkk;
-        if (lane == k) { mypiv = piv; myrinv = rinv; }
-        a[k] = (lane == k) ? lkk : a[k] * rinv;
+        for (int k = 0; k < 32; ++k) {
+            const double piv = shfl_d(a[k], k);
+            if (!(piv > 0.0)) ok = 0;
+            double lkk, rinv;
+            sqrt_rsqrt(piv, lkk, rinv);
+            if (lane == k) { mypiv = piv; myrinv = rinv; }
+            a[k] = (lane == k) ? lkk : a[k] * rinv;
 #pragma unroll
-        for (int c = k + 1; c < 32; ++c) {
-            const double lc = shfl_d(a[k], c);
-            a[c] = fma(-a[k], lc, a[c]);
+            for (int c = k + 1; c < 32; ++c) {
+                const double lc = shfl_d(a[k], c);
+                a[c] = fma(-a[k], lc, a[c]);
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+            if (c > lane) a[c] = 0.0;
+            T[lane * 32 + c] = a[c];
+            sL[lane * 33 + c] = a[c];
         }
     }
+    __syncwarp();
+    {   // forward substitution on the identity by columns: lane = column of Y, s[r] = running right-hand side
+        double s[32];
 #pragma unroll
-    for (int c = 0; c < 32; ++c) {
-        if (c > lane) a[c] = 0.0;
-        T[lane * 32 + c] = a[c];
-    }
-    // forward substitution on the identity, lane = column of Y
+        for (int r = 0; r < 32; ++r) s[r] = (r == lane) ? 1.0 : 0.0;
 #pragma unroll
-    for (int r = 0; r < 32; ++r) {
-        double s = (r == lane) ? 1.0 : 0.0;
+        for (int k = 0; k < 32; ++k) {
+            const double yk = s[k] * shfl_d(myrinv, k);
+            sYinv[k * TRAIN_LDY + lane] = yk;
+            Mjj[lane * 32 + k] = yk;                 // M_jj[c][k] = Y[k][c]
 #pragma unroll
-        for (int k = 0; k < r; ++k) s = fma(-shfl_d(a[k], r), sYinv[k * TRAIN_LDY + lane], s);
-        const double yv = s * shfl_d(myrinv, r);
-        sYinv[r * TRAIN_LDY + lane] = yv;
-        Mjj[lane * 32 + r] = yv;                 // M_jj[c][r] = Y[r][c]
+            for (int r = k + 1; r < 32; ++r) s[r] = fma(-sL[r * 33 + k], yk, s[r]);
+        }
     }
     return warp_sum(0.5 * log(mypiv));
 }
 
+__device__ __forceinline__ void prefetch_tile(const double* T, int lane) {      // 8 KB = 64 lines of 128 bytes
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(T + lane * 16));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(T + 512 + lane * 16));
+}
+
 // d(kernel)/d(log ell_m) = gfun(sq) * D_m with D_m the squared scaled difference in dimension m (scikit-learn
 // kernels.py: Matern.__call__ / RBF.__call__ with eval_gradient=True); kval = the kernel value itself.
-__device__ __forceinline__ void kernel_and_gfun(int kind, double sq, double& kval, double& gfun) {
-    if (kind == 3) {
-        kval = exp(-0.5 * sq);
+template <int KIND>
+__device__ __forceinline__ void kernel_and_gfun(double sq, double& kval, double& gfun) {
+    if (KIND == 3) {
+        kval = exp_neg(0.5 * sq);
         gfun = kval;
         return;
     }
-    const double r = sqrt(sq);
-    if (kind == 0) {
-        kval = exp(-r);
-        gfun = (r > 0.0) ? kval / r : 0.0;
-    } else if (kind == 1) {
+    const double r = sqrt_pos(sq);            // 1e-150 instead of 0 at coincident points: their D_m are exactly 0
+    if (KIND == 0) {
+        kval = exp_neg(r);
+        gfun = kval / r;
+    } else if (KIND == 1) {
         const double t = r * 1.7320508075688772;
-        const double e = exp(-t);
-        kval = (1.0 + t) * e;
+        const double e = exp_neg(t);
+        kval = fma(t, e, e);
         gfun = 3.0 * e;
     } else {
         const double t = r * 2.23606797749979;
-        const double e = exp(-t);
-        kval = (1.0 + t + t * t / 3.0) * e;
+        const double e = exp_neg(t);
+        kval = fma(t * t, 1.0 / 3.0, 1.0 + t) * e;
         gfun = (5.0 / 3.0) * (t + 1.0) * e;
     }
 }
 
-__global__ void __launch_bounds__(512, 1) gp_lml_kernel(const LmlParams P) {
+// ---- launch 1: K + alpha I as lower tiles (identity padding past N).  grid (ntri, B), 256 threads, 4 elements each.
+template <int KIND>
+__global__ void __launch_bounds__(256) gp_kbuild_kernel(const LmlParams P) {
+    __shared__ double sInv[TRAIN_MAX_D];
+    __shared__ double sXp[32 * TRAIN_MAX_D], sXq[32 * TRAIN_MAX_D];
+    const int N = P.N, d = P.d, nt = (N + 31) / 32, ntri = nt * (nt + 1) / 2;
+    const int tI = blockIdx.x, tid = threadIdx.x;
+    const long long b = blockIdx.y;
+    int ti = (int)((sqrt(8.0 * tI + 1.0) - 1.0) * 0.5);
+    while ((ti + 1) * (ti + 2) / 2 <= tI) ++ti;
+    while (ti * (ti + 1) / 2 > tI) --ti;
+    const int tj = tI - ti * (ti + 1) / 2;
+    const double* th = P.theta + b * P.nh;
+    if (tid < d) sInv[tid] = exp(th[tid]);
+    __syncthreads();
+    for (int idx = tid; idx < 32 * d; idx += 256) {          // X / length_scale for the tile's 32 rows and 32 columns
+        const int r = idx / d, m = idx - r * d;
+        sXp[idx] = P.X[min(ti * 32 + r, N - 1) * d + m] / sInv[m];
+        sXq[m * 32 + r] = P.X[min(tj * 32 + r, N - 1) * d + m] / sInv[m];      // transposed: lanes read consecutive columns
+    }
+    const double cst = P.has_const ? exp(th[d]) : 0.0;
+    const double eta = P.has_white ? exp(th[d + (P.has_const ? 1 : 0)]) : 0.0;
+    __syncthreads();
+    double* T = P.Kt + ((size_t)b * ntri + tI) * 1024;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const int e = tid + 256 * u, r = e >> 5, c = e & 31, p = ti * 32 + r, q = tj * 32 + c;
+        double sq = 0.0;
+        for (int m = 0; m < d; ++m) {
+            const double df = sXp[r * d + m] - sXq[m * 32 + c];
+            sq = fma(df, df, sq);
+        }
+        double kv, gf;
+        kernel_and_gfun<KIND>(sq, kv, gf);
+        const double dg = (p == q) ? 1.0 : 0.0;
+        T[e] = (p < N && q < N) ? kv + cst + dg * (eta + P.alpha) : dg;
+    }
+}
+
+// ---- launch 2: factorisation, inverse factor, K^-1, alpha, LML.  One CTA per problem, persistent.
+__global__ void __launch_bounds__(512, 1) gp_factor_kernel(const LmlParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int N = P.N, d = P.d, nt = (N + 31) / 32, Np = nt * 32, ntri = nt * (nt + 1) / 2;
+    const int N = P.N, nt = (N + 31) / 32, Np = nt * 32, ntri = nt * (nt + 1) / 2;
     const int tid = threadIdx.x, nth = blockDim.x, lane = tid & 31, warp = tid >> 5, NW = nth >> 5;
-    double* sXs = reinterpret_cast<double*>(smem_raw);            // [N][d] design / length scale
-    double* sY = sXs + ((N * d + 1) & ~1);                        // [Np] targets, zero padded
+    double* sY = reinterpret_cast<double*>(smem_raw);             // [Np] targets, zero padded
     double* sZ = sY + Np;                                         // [Np] L^-1 y
     double* sAl = sZ + Np;                                        // [Np] K^-1 y
     double* sYinv = sAl + Np;                                     // [32][TRAIN_LDY] inverse of the diagonal tile
-    double* sRed = sYinv + 32 * TRAIN_LDY;                        // [NW][TRAIN_MAX_D + 4]
-    double* sHyp = sRed + NW * (TRAIN_MAX_D + 4);                 // [2 * TRAIN_MAX_D + 8]: 1/ell, c, eta, logdet
-    int* sTi = reinterpret_cast<int*>(sHyp + 2 * TRAIN_MAX_D + 8);
+    double* sL = sYinv + 32 * TRAIN_LDY;                          // [32][33] the factorised diagonal tile
+    double* sRed = sL + 32 * 33;                                  // [NW + 8]
+    int* sTi = reinterpret_cast<int*>(sRed + NW + 8);
     int* sTj = sTi + ntri;
     int* sOk = sTj + ntri;
 
-    double* Lt = P.scratch + (long long)blockIdx.x * P.scratch_stride;      // lower tiles (i, j) at tri_idx(i, j)
-    double* Mt = Lt + (size_t)ntri * 1024;                                  // M tile (i', k) at tri_idx(k, i')
+    double* Mt = P.scratch + (long long)blockIdx.x * P.scratch_stride;      // M tile (i', k) at tri_idx(k, i')
 
     for (int i = tid; i < nt; i += nth)
         for (int j = 0; j <= i; ++j) {
@@ -208,42 +294,22 @@ __global__ void __launch_bounds__(512, 1) gp_lml_kernel(const LmlParams P) {
 
     for (long long b = blockIdx.x; b < P.B; b += gridDim.x) {
         __syncthreads();
-        const double* th = P.theta + b * P.nh;
-        if (tid < d) sHyp[tid] = exp(th[tid]);
-        if (tid == 0) {
-            sHyp[TRAIN_MAX_D] = P.has_const ? exp(th[d]) : 0.0;
-            sHyp[TRAIN_MAX_D + 1] = P.has_white ? exp(th[d + (P.has_const ? 1 : 0)]) : 0.0;
-            *sOk = 1;
-        }
-        __syncthreads();
-        const double cst = sHyp[TRAIN_MAX_D], eta = sHyp[TRAIN_MAX_D + 1];
+#ifdef TRAIN_TIMING
+        long long t0_ = clock64();
+#endif
+        double* Lt = P.Kt + (size_t)b * ntri * 1024;              // lower tiles (i, j) at tri_idx(i, j)
         {
             const long long yrow = P.y_index ? P.y_index[b] : b;
-            for (int idx = tid; idx < N * d; idx += nth) sXs[idx] = P.X[idx] / sHyp[idx % d];     // X / length_scale
             for (int idx = tid; idx < Np; idx += nth) sY[idx] = idx < N ? P.Y[yrow * N + idx] : 0.0;
+            if (tid == 0) *sOk = 1;
         }
         __syncthreads();
+        TR_T(0);
 
-        // ---- K + alpha I as lower tiles (identity padding past N)
-        for (int e = tid; e < ntri * 1024; e += nth) {
-            const int tI = e >> 10, p = sTi[tI] * 32 + ((e >> 5) & 31), q = sTj[tI] * 32 + (e & 31);
-            double val = (p == q) ? 1.0 : 0.0;
-            if (p < N && q < N) {
-                double sq = 0.0;
-                for (int m = 0; m < d; ++m) {
-                    const double df = sXs[p * d + m] - sXs[q * d + m];
-                    sq = fma(df, df, sq);
-                }
-                double kv, gf;
-                kernel_and_gfun(P.kind, sq, kv, gf);
-                val = kv + cst;
-                if (p == q) val += eta + P.alpha;
-            }
-            Lt[e] = val;
-        }
-        __syncthreads();
-
-        // ---- left-looking blocked Cholesky of [[K, I], [I, 0]]: nt units per panel
+        // ---- left-looking blocked Cholesky of [[K, I], [I, 0]]: nt units per panel.
+        // The diagonal tile of panel j + 1 is swept one panel ahead (all k < j, by the warp whose own unit is the
+        // shortest), so that warp 0 only adds k = j - 1 before it factorises: the serial part of a panel is one product
+        // + potrf instead of j products + potrf.
         double logdet = 0.0;
         for (int j = 0; j < nt; ++j) {
             const int nreg = nt - j;          // units 0 .. nreg-1: tiles (j + u, j) of L; nreg .. nt-1: M tiles (u - nreg, j)
@@ -254,24 +320,42 @@ __global__ void __launch_bounds__(512, 1) gp_lml_kernel(const LmlParams P) {
                     const int i = j + u;
                     T = Lt + (size_t)tri_idx(i, j) * 1024;
                     acc_load(acc, T, lane);
-                    for (int k = 0; k < j; ++k)
+                    for (int k = (u == 0 && j > 0) ? j - 1 : 0; k < j; ++k) {
+                        if (k + 1 < j) prefetch_tile(Lt + (size_t)tri_idx(i, k + 1) * 1024, lane);
                         tile_nt<true, 32>(acc, Lt + (size_t)tri_idx(i, k) * 1024, Lt + (size_t)tri_idx(j, k) * 1024, lane);
+                    }
                 } else {
                     const int ip = u - nreg;
                     T = Mt + (size_t)tri_idx(j, ip) * 1024;
                     acc_zero(acc);
-                    for (int k = ip; k < j; ++k)
+                    for (int k = ip; k < j; ++k) {
+                        if (k + 1 < j) prefetch_tile(Mt + (size_t)tri_idx(k + 1, ip) * 1024, lane);
                         tile_nt<true, 32>(acc, Mt + (size_t)tri_idx(k, ip) * 1024, Lt + (size_t)tri_idx(j, k) * 1024, lane);
+                    }
                 }
                 acc_store(acc, T, lane);
                 if (u == 0) {                 // warp 0 owns the diagonal tile: factorise + invert it right away
                     __syncwarp();
+                    TR_T(1);
                     int ok = 1;
-                    logdet += warp_potrf_inv(T, sYinv, Mt + (size_t)tri_idx(j, j) * 1024, lane, ok);
+                    logdet += warp_potrf_inv(T, sYinv, sL, Mt + (size_t)tri_idx(j, j) * 1024, lane, ok);
                     if (!ok && lane == 0) *sOk = 0;
+                    TR_T(2);
                 }
             }
+            if (warp == NW - 1 && j + 1 < nt && j > 0) {        // look-ahead: tile (j+1, j+1) -= sum_{k<j} L(j+1,k) L(j+1,k)^T
+                double acc[4][4][2];
+                double* T = Lt + (size_t)tri_idx(j + 1, j + 1) * 1024;
+                acc_load(acc, T, lane);
+                for (int k = 0; k < j; ++k) {
+                    const double* A = Lt + (size_t)tri_idx(j + 1, k) * 1024;
+                    if (k + 1 < j) prefetch_tile(A + 1024, lane);
+                    tile_nt<true, 32>(acc, A, A, lane);
+                }
+                acc_store(acc, T, lane);
+            }
             __syncthreads();
+            TR_T(3);
             for (int u = warp; u < nt; u += NW) {
                 if (u == 0) continue;
                 double* T = (u < nreg) ? Lt + (size_t)tri_idx(j + u, j) * 1024 : Mt + (size_t)tri_idx(j, u - nreg) * 1024;
@@ -282,6 +366,7 @@ __global__ void __launch_bounds__(512, 1) gp_lml_kernel(const LmlParams P) {
                 acc_store(acc, T, lane);
             }
             __syncthreads();
+            TR_T(4);
         }
 
         // ---- z = L^-1 y = M^T y   (thread = element of z)
@@ -297,14 +382,23 @@ __global__ void __launch_bounds__(512, 1) gp_lml_kernel(const LmlParams P) {
             sZ[idx] = s;
         }
         __syncthreads();
+        TR_T(5);
         // ---- a = L^-T z = M z      (warp = row)
         for (int row = warp; row < Np; row += NW) {
             const int ip = row >> 5, r = row & 31;
             double s = 0.0;
             for (int k = ip; k < nt; ++k) s = fma(Mt[(size_t)tri_idx(k, ip) * 1024 + r * 32 + lane], sZ[k * 32 + lane], s);
             s = warp_sum(s);
-            if (lane == 0) sAl[row] = s;
+            if (lane == 0) {
+                sAl[row] = s;
+                P.Ab[(size_t)b * Np + row] = s;
+            }
         }
+        TR_T(6);
+        double qd = 0.0;
+        for (int idx = tid; idx < Np; idx += nth) qd = fma(sZ[idx], sZ[idx], qd);
+        qd = warp_sum(qd);
+        if (lane == 0) sRed[warp] = qd;
         if (P.L_out != nullptr) {       // the fitted state scikit-learn keeps (_gpr.py:335-366): L_, alpha_ and the LML
             __syncthreads();
             double* Lo = P.L_out + (size_t)b * N * N;
@@ -312,97 +406,113 @@ __global__ void __launch_bounds__(512, 1) gp_lml_kernel(const LmlParams P) {
                 const int p = e / N, q = e - p * N;
                 Lo[e] = (q <= p) ? Lt[(size_t)tri_idx(p >> 5, q >> 5) * 1024 + (p & 31) * 32 + (q & 31)] : 0.0;
             }
-            double qd = 0.0;
-            for (int idx = tid; idx < Np; idx += nth) {
-                if (idx < N) P.alpha_out[(size_t)b * N + idx] = sAl[idx];
-                qd = fma(sZ[idx], sZ[idx], qd);
-            }
-            qd = warp_sum(qd);
-            if (lane == 0) sRed[warp] = qd;
-            __syncthreads();
-            if (tid == 0) {
-                double s = 0.0;
-                for (int w = 0; w < NW; ++w) s += sRed[w];
-                P.lml[b] = *sOk ? (-0.5 * s - logdet - 0.5 * N * 1.8378770664093453) : -INFINITY;
-            }
-            continue;
-        }
-        // ---- K^-1 = M M^T, lower tiles, written over L
-        for (int tI = warp; tI < ntri; tI += NW) {
-            const int a = sTi[tI], bb = sTj[tI];
-            double acc[4][4][2];
-            acc_zero(acc);
-            for (int k = a; k < nt; ++k)
-                tile_nt<false, 32>(acc, Mt + (size_t)tri_idx(k, a) * 1024, Mt + (size_t)tri_idx(k, bb) * 1024, lane);
-            acc_store(acc, Lt + (size_t)tI * 1024, lane);
-        }
-        __syncthreads();
-
-        // ---- gradient: 1/2 sum_pq (a_p a_q - Kinv_pq) dK_pq/dtheta_m over the lower triangle (off-diagonal counted twice)
-        double g[TRAIN_MAX_D];
-#pragma unroll
-        for (int m = 0; m < TRAIN_MAX_D; ++m) g[m] = 0.0;
-        double gc = 0.0, gw = 0.0, qd = 0.0;
-        for (int e = tid; e < ntri * 1024; e += nth) {
-            const int tI = e >> 10, p = sTi[tI] * 32 + ((e >> 5) & 31), q = sTj[tI] * 32 + (e & 31);
-            if (p < N && q <= p) {
-                const double wv = fma(sAl[p], sAl[q], -Lt[e]);
-                if (p == q) {
-                    gw += wv;
-                    gc += wv;            // D = 0 on the diagonal: no length-scale term
-                } else {
-                    double D[TRAIN_MAX_D];
-                    double sq = 0.0;
-#pragma unroll
-                    for (int m = 0; m < TRAIN_MAX_D; ++m) {
-                        if (m < d) {
-                            const double df = sXs[p * d + m] - sXs[q * d + m];
-                            D[m] = df * df;
-                            sq += D[m];
-                        }
+            for (int idx = tid; idx < N; idx += nth) P.alpha_out[(size_t)b * N + idx] = sAl[idx];
+        } else {
+            // ---- K^-1 = M M^T, lower tiles, written over L
+            for (int tI = warp; tI < ntri; tI += NW) {
+                const int a = sTi[tI], bb = sTj[tI];
+                double acc[4][4][2];
+                acc_zero(acc);
+                for (int k = a; k < nt; ++k) {
+                    if (k + 1 < nt) {
+                        prefetch_tile(Mt + (size_t)tri_idx(k + 1, a) * 1024, lane);
+                        prefetch_tile(Mt + (size_t)tri_idx(k + 1, bb) * 1024, lane);
                     }
-                    double kv, gf;
-                    kernel_and_gfun(P.kind, sq, kv, gf);
-                    const double w2 = 2.0 * wv;
-                    gc += w2;
-                    const double wg = w2 * gf;
-#pragma unroll
-                    for (int m = 0; m < TRAIN_MAX_D; ++m)
-                        if (m < d) g[m] = fma(wg, D[m], g[m]);
+                    tile_nt<false, 32>(acc, Mt + (size_t)tri_idx(k, a) * 1024, Mt + (size_t)tri_idx(k, bb) * 1024, lane);
                 }
+                acc_store(acc, Lt + (size_t)tI * 1024, lane);
             }
+            __syncthreads();
         }
-        for (int idx = tid; idx < Np; idx += nth) qd = fma(sZ[idx], sZ[idx], qd);
+        TR_T(7);
+        if (tid == 0) {
+            double s = 0.0;
+            for (int w = 0; w < NW; ++w) s += sRed[w];
+            P.lml[b] = *sOk ? (-0.5 * s - logdet - 0.5 * N * 1.8378770664093453) : -INFINITY;     // log(2 pi)
+        }
+    }
+}
+
+// ---- launch 3: grad_m = 1/2 sum_pq (a_p a_q - Kinv_pq) dK_pq/dtheta_m over the lower triangle (off-diagonal entries
+// counted twice).  One CTA of 512 threads per problem, warp = row p, lanes = columns q <= p; deterministic reduction.
+template <int KIND, int DMAX>
+__global__ void __launch_bounds__(512, 2) gp_grad_kernel(const LmlParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int N = P.N, d = P.d, nt = (N + 31) / 32, Np = nt * 32, ntri = nt * (nt + 1) / 2;
+    const int tid = threadIdx.x, nth = blockDim.x, lane = tid & 31, warp = tid >> 5, NW = nth >> 5;
+    const long long b = blockIdx.x;
+    double* sXs = reinterpret_cast<double*>(smem_raw);            // [N][d] design / length scale
+    double* sAl = sXs + ((N * d + 1) & ~1);                       // [Np]
+    double* sRed = sAl + Np;                                      // [NW <= 32][TRAIN_MAX_D + 2]
+    double* sHyp = sRed + 32 * (TRAIN_MAX_D + 2);                 // [TRAIN_MAX_D + 4]
+    const double* th = P.theta + b * P.nh;
+    if (tid < d) sHyp[tid] = exp(th[tid]);
+    __syncthreads();
+    for (int idx = tid; idx < N * d; idx += nth) sXs[idx] = P.X[idx] / sHyp[idx % d];
+    for (int idx = tid; idx < Np; idx += nth) sAl[idx] = P.Ab[(size_t)b * Np + idx];
+    __syncthreads();
+    const double* Kinv = P.Kt + (size_t)b * ntri * 1024;
+    double g[DMAX];          // DMAX = 8 or 16 >= d: accumulators stay in registers
 #pragma unroll
-        for (int m = 0; m < TRAIN_MAX_D; ++m) {
-            const double s = warp_sum(g[m]);
-            if (lane == 0) sRed[warp * (TRAIN_MAX_D + 4) + m] = s;
-        }
-        gc = warp_sum(gc);
-        gw = warp_sum(gw);
-        qd = warp_sum(qd);
-        if (lane == 0) {
-            sRed[warp * (TRAIN_MAX_D + 4) + TRAIN_MAX_D] = gc;
-            sRed[warp * (TRAIN_MAX_D + 4) + TRAIN_MAX_D + 1] = gw;
-            sRed[warp * (TRAIN_MAX_D + 4) + TRAIN_MAX_D + 2] = qd;
-        }
-        __syncthreads();
-        if (warp == 0) {
-            const int ok = *sOk;
-            if (lane < TRAIN_MAX_D + 3) {
-                double s = 0.0;
-                for (int w = 0; w < NW; ++w) s += sRed[w * (TRAIN_MAX_D + 4) + lane];
-                if (lane < d) P.grad[b * P.nh + lane] = ok ? 0.5 * s : 0.0;
-                int pos = d;
-                if (P.has_const) {
-                    if (lane == TRAIN_MAX_D) P.grad[b * P.nh + pos] = ok ? 0.5 * s * cst : 0.0;
-                    ++pos;
-                }
-                if (P.has_white && lane == TRAIN_MAX_D + 1) P.grad[b * P.nh + pos] = ok ? 0.5 * s * eta : 0.0;
-                if (lane == TRAIN_MAX_D + 2)
-                    P.lml[b] = ok ? (-0.5 * s - logdet - 0.5 * N * 1.8378770664093453) : -INFINITY;     // log(2 pi)
+    for (int m = 0; m < DMAX; ++m) g[m] = 0.0;
+    double gc = 0.0, gw = 0.0;
+    // rows are dealt in pairs (j, N-1-j): every pair has N + 1 columns, so the warps are balanced
+    for (int it = 0;; ++it) {
+        const int jp = warp + (it >> 1) * NW;
+        if (jp >= ((N + 1) >> 1)) break;
+        const int p = (it & 1) ? N - 1 - jp : jp;
+        if ((it & 1) && p == jp) continue;             // the middle row of an odd N is its own partner
+        const double ap = sAl[p];
+        const double* xp = sXs + p * d;
+        const double* Krow = Kinv + (size_t)tri_idx(p >> 5, 0) * 1024 + (p & 31) * 32;
+#pragma unroll 2
+        for (int q0 = 0; q0 <= p; q0 += 32) {
+            const int q = q0 + lane, qc = min(q, p);
+            const double wv = fma(ap, sAl[qc], -Krow[(size_t)(q0 >> 5) * 1024 + (qc & 31)]);
+            const double wd = (q == p) ? wv : 0.0;                      // diagonal: constant and white terms only
+            const double w2 = (q < p) ? 2.0 * wv : 0.0;                 // strictly lower: counted twice
+            gw += wd;
+            gc += wd + w2;
+            const double* xq = sXs + qc * d;
+            double sq = 0.0;
+            for (int m = 0; m < d; ++m) {
+                const double df = xp[m] - xq[m];
+                sq = fma(df, df, sq);
             }
+            double kv, gf;
+            kernel_and_gfun<KIND>(sq, kv, gf);
+            const double wg = w2 * gf;
+#pragma unroll
+            for (int m = 0; m < DMAX; ++m)
+                if (m < d) {
+                    const double df = xp[m] - xq[m];
+                    g[m] = fma(wg * df, df, g[m]);
+                }
         }
+    }
+#pragma unroll
+    for (int m = 0; m < DMAX; ++m) {
+        const double s = warp_sum(g[m]);
+        if (lane == 0) sRed[warp * (TRAIN_MAX_D + 2) + m] = s;
+    }
+    gc = warp_sum(gc);
+    gw = warp_sum(gw);
+    if (lane == 0) {
+        sRed[warp * (TRAIN_MAX_D + 2) + TRAIN_MAX_D] = gc;
+        sRed[warp * (TRAIN_MAX_D + 2) + TRAIN_MAX_D + 1] = gw;
+    }
+    __syncthreads();
+    if (warp == 0 && lane < TRAIN_MAX_D + 2) {
+        const bool ok = P.lml[b] > -INFINITY;           // not positive definite: (-inf, zero gradient), _gpr.py:586-589
+        double s = 0.0;
+        for (int w = 0; w < NW; ++w) s += sRed[w * (TRAIN_MAX_D + 2) + lane];
+        if (lane < d) P.grad[b * P.nh + lane] = ok ? 0.5 * s : 0.0;
+        int pos = d;
+        if (P.has_const) {
+            if (lane == TRAIN_MAX_D) P.grad[b * P.nh + pos] = ok ? 0.5 * s * exp(th[pos]) : 0.0;
+            ++pos;
+        }
+        if (P.has_white && lane == TRAIN_MAX_D + 1) P.grad[b * P.nh + pos] = ok ? 0.5 * s * exp(th[pos]) : 0.0;
     }
 }
 
