@@ -18,13 +18,15 @@
 // (i', k) exist for i' <= k and their sweeps start at k = i'), its Schur complement is -M M^T = -K^-1.  Every tile
 // update is an "NT" product  acc -= A_tile * B_tile^T  on the FP64 tensor pipe (mma.sync m8n8k4, SASS DMMA), operands
 // read straight from the row-major tiles (32-byte sectors, fully used).  Per panel j there are exactly nt independent
-// units (nt - j tiles of L, j tiles of M), one per warp; the diagonal tile is factorised and inverted by warp 0
-// (lane = row, shuffles), and the panel solve is one more NT product with the explicit 32 x 32 inverse.
+// units (nt - j tiles of L, j tiles of M), one per warp; the diagonal tile is factorised by warp 0 with K4's blocked
+// potrf (8-column panels, DMMA trailing updates, 8 x 8 inverses) and the panel solve is K4's blocked triangular solve on
+// DMMA; M_jj = L_jj^-T is that same solve applied to the identity tile.
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
 
+#include "chol_pipe.cuh"       // warp_potrf_blocked / strip_trsm_blocked: the diagonal-tile factorisation and panel solve of K4
 #include "common.cuh"
 #include "gp_predict.cuh"      // exp_neg / sqrt_pos: branch-free exp(-x), sqrt(x) (<= 2 ulp)
 
@@ -32,7 +34,6 @@ namespace bi {
 
 constexpr int TRAIN_MAX_D = 16;       // length scales per kernel (parameters of the model)
 constexpr int TRAIN_MAX_NT = 31;      // N <= 992
-constexpr int TRAIN_LDY = 36;         // row stride of the diagonal-tile inverse in shared memory (bank-conflict free)
 
 struct LmlParams {
     const double* X;        // (N, d) design, row-major
@@ -67,7 +68,7 @@ __host__ inline size_t lml_tiles_doubles(int N) {        // per problem: lower t
 }
 __host__ inline size_t lml_factor_smem_bytes(int N, int nwarps) {
     const int nt = (N + 31) / 32, Np = nt * 32;
-    size_t dbl = 3 * (size_t)Np + 32 * TRAIN_LDY + 32 * 33 + (size_t)nwarps + 8;
+    size_t dbl = 3 * (size_t)Np + 1024 + 256 + 32 + 32 * 33 + (size_t)nwarps + 8;
     return dbl * 8 + (size_t)nt * (nt + 1) / 2 * 2 * sizeof(int) + 16;
 }
 __host__ inline size_t lml_grad_smem_bytes(int N, int d) {
@@ -129,74 +130,6 @@ __device__ __forceinline__ void acc_store(const double (&acc)[4][4][2], double* 
 #pragma unroll
         for (int nf = 0; nf < 4; ++nf)
             *reinterpret_cast<double2*>(p + mf * 256 + nf * 8) = make_double2(acc[mf][nf][0], acc[mf][nf][1]);
-}
-
-// sqrt(s) and 1/sqrt(s) together (s > 0): MUFU.RSQ64H seed (2^-20) + two coupled Goldschmidt steps (-> 2^-80, i.e.
-// rounding-limited, <= 2 ulp).  No final correction: every dependent FP64 instruction of the factorisation's column
-// chain costs ~100 cycles while the other warps keep the FP64 pipe busy with DMMAs.
-__device__ __forceinline__ void sqrt_rsqrt(double s, double& root, double& rinv) {
-    double y;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(s));
-    double g = s * y, h = 0.5 * y;
-#pragma unroll
-    for (int it = 0; it < 2; ++it) {
-        const double r = fma(-g, h, 0.5);
-        g = fma(g, r, g);
-        h = fma(h, r, h);
-    }
-    root = g;
-    rinv = h + h;
-}
-
-// Warp 0: factorise the 32 x 32 diagonal tile T in place (lower, zeros above), write Y = L_jj^-1 row-major into sYinv
-// (stride TRAIN_LDY) and M_jj = Y^T into Mjj.  sL: 32 x 33 scratch for L_jj.  Returns sum log L_kk over the tile's rows;
-// ok = 0 on a non-positive pivot.
-__device__ __noinline__ double warp_potrf_inv(double* T, double* sYinv, double* sL, double* Mjj, int lane, int& ok) {
-    double mypiv = 1.0, myrinv = 1.0;
-    {
-        double a[32];      // lane = row
-        const double4* row = reinterpret_cast<const double4*>(T + lane * 32);
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const double4 v = row[q];
-            a[4 * q] = v.x; a[4 * q + 1] = v.y; a[4 * q + 2] = v.z; a[4 * q + 3] = v.w;
-        }
-#pragma unroll
-        for (int k = 0; k < 32; ++k) {
-            const double piv = shfl_d(a[k], k);
-            if (!(piv > 0.0)) ok = 0;
-            double lkk, rinv;
-            sqrt_rsqrt(piv, lkk, rinv);
-            if (lane == k) { mypiv = piv; myrinv = rinv; }
-            a[k] = (lane == k) ? lkk : a[k] * rinv;
-#pragma unroll
-            for (int c = k + 1; c < 32; ++c) {
-                const double lc = shfl_d(a[k], c);
-                a[c] = fma(-a[k], lc, a[c]);
-            }
-        }
-#pragma unroll
-        for (int c = 0; c < 32; ++c) {
-            if (c > lane) a[c] = 0.0;
-            T[lane * 32 + c] = a[c];
-            sL[lane * 33 + c] = a[c];
-        }
-    }
-    __syncwarp();
-    {   // forward substitution on the identity by columns: lane = column of Y, s[r] = running right-hand side
-        double s[32];
-#pragma unroll
-        for (int r = 0; r < 32; ++r) s[r] = (r == lane) ? 1.0 : 0.0;
-#pragma unroll
-        for (int k = 0; k < 32; ++k) {
-            const double yk = s[k] * shfl_d(myrinv, k);
-            sYinv[k * TRAIN_LDY + lane] = yk;
-            Mjj[lane * 32 + k] = yk;                 // M_jj[c][k] = Y[k][c]
-#pragma unroll
-            for (int r = k + 1; r < 32; ++r) s[r] = fma(-sL[r * 33 + k], yk, s[r]);
-        }
-    }
-    return warp_sum(0.5 * log(mypiv));
 }
 
 __device__ __forceinline__ void prefetch_tile(const double* T, int lane) {      // 8 KB = 64 lines of 128 bytes
@@ -277,8 +210,10 @@ __global__ void __launch_bounds__(512, 1) gp_factor_kernel(const LmlParams P) {
     double* sY = reinterpret_cast<double*>(smem_raw);             // [Np] targets, zero padded
     double* sZ = sY + Np;                                         // [Np] L^-1 y
     double* sAl = sZ + Np;                                        // [Np] K^-1 y
-    double* sYinv = sAl + Np;                                     // [32][TRAIN_LDY] inverse of the diagonal tile
-    double* sL = sYinv + 32 * TRAIN_LDY;                          // [32][33] the factorised diagonal tile
+    double* sLjj = sAl + Np;                                      // [1024] L_jj as B-operand fragments (blocked panel solve)
+    double* sLinvB = sLjj + 1024;                                 // [256]  inverses of its four 8 x 8 diagonal blocks
+    double* sRinv = sLinvB + 256;                                 // [32]   1 / L_kk
+    double* sL = sRinv + 32;                                      // [32][33] the diagonal tile, row-major
     double* sRed = sL + 32 * 33;                                  // [NW + 8]
     int* sTi = reinterpret_cast<int*>(sRed + NW + 8);
     int* sTj = sTi + ntri;
@@ -334,12 +269,18 @@ __global__ void __launch_bounds__(512, 1) gp_factor_kernel(const LmlParams P) {
                     }
                 }
                 acc_store(acc, T, lane);
-                if (u == 0) {                 // warp 0 owns the diagonal tile: factorise + invert it right away
+                if (u == 0) {                 // warp 0 owns the diagonal tile: blocked factorisation as in K4
                     __syncwarp();
                     TR_T(1);
-                    int ok = 1;
-                    logdet += warp_potrf_inv(T, sYinv, sL, Mt + (size_t)tri_idx(j, j) * 1024, lane, ok);
-                    if (!ok && lane == 0) *sOk = 0;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) sL[lane * 33 + c] = T[lane * 32 + c];
+                    __syncwarp();
+                    double mypiv, quad;
+                    if (warp_potrf_blocked(sL, sLjj, sLinvB, sRinv, lane, mypiv, -1, quad) != 0 && lane == 0) *sOk = 0;
+                    __syncwarp();
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) T[lane * 32 + c] = (c <= lane) ? sL[lane * 33 + c] : 0.0;
+                    logdet += warp_sum(0.5 * log(mypiv));
                     TR_T(2);
                 }
             }
@@ -356,14 +297,36 @@ __global__ void __launch_bounds__(512, 1) gp_factor_kernel(const LmlParams P) {
             }
             __syncthreads();
             TR_T(3);
+            // panel solve X = T L_jj^-T, blocked (L_jj + its 8 x 8 inverses), two 16-row strips per tile; warp 0's unit
+            // is the identity tile: M_jj = L_jj^-T
             for (int u = warp; u < nt; u += NW) {
-                if (u == 0) continue;
-                double* T = (u < nreg) ? Lt + (size_t)tri_idx(j + u, j) * 1024 : Mt + (size_t)tri_idx(j, u - nreg) * 1024;
-                double acc[4][4][2];
-                acc_zero(acc);
-                tile_nt<false, TRAIN_LDY>(acc, T, sYinv, lane);       // T * L_jj^-T
-                __syncwarp();
-                acc_store(acc, T, lane);
+                double* T = (u == 0) ? Mt + (size_t)tri_idx(j, j) * 1024
+                          : (u < nreg) ? Lt + (size_t)tri_idx(j + u, j) * 1024 : Mt + (size_t)tri_idx(j, u - nreg) * 1024;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    double c[2][4][2], xa[2][8];
+                    double* p = T + (16 * h + (lane >> 2)) * 32 + 2 * (lane & 3);
+#pragma unroll
+                    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                        for (int nf = 0; nf < 4; ++nf) {
+                            if (u == 0) {
+                                const int r = 16 * h + 8 * mi + (lane >> 2), cc = 8 * nf + 2 * (lane & 3);
+                                c[mi][nf][0] = (r == cc) ? 1.0 : 0.0;
+                                c[mi][nf][1] = (r == cc + 1) ? 1.0 : 0.0;
+                            } else {
+                                const double2 v = *reinterpret_cast<const double2*>(p + mi * 256 + nf * 8);
+                                c[mi][nf][0] = v.x;
+                                c[mi][nf][1] = v.y;
+                            }
+                        }
+                    strip_trsm_blocked(c, xa, sLjj + lane, sLinvB + lane, lane);
+#pragma unroll
+                    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                        for (int nf = 0; nf < 4; ++nf)
+                            *reinterpret_cast<double2*>(p + mi * 256 + nf * 8) = make_double2(c[mi][nf][0], c[mi][nf][1]);
+                }
             }
             __syncthreads();
             TR_T(4);
