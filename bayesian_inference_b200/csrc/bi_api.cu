@@ -1165,7 +1165,7 @@ int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, in
                       int32_t has_white, double alpha, int32_t device, bi_trainer* out) {
     if (!out) return BI_E_ARG;
     *out = nullptr;
-    if (!X || !Y || N < 1 || N > 32 * TRAIN_MAX_NT || d < 1 || d > TRAIN_MAX_D || n_y < 1 || kind < 0 || kind > 3 || !(alpha >= 0.0))
+    if (!X || !Y || N < 1 || N + 1 > 32 * TRAIN_MAX_NT || d < 1 || d > TRAIN_MAX_D || n_y < 1 || kind < 0 || kind > 3 || !(alpha >= 0.0))
         return BI_E_ARG;
     bi_trainer t = new bi_trainer_s();
     t->device = device; t->N = N; t->d = d; t->n_y = n_y; t->kind = kind;
@@ -1177,7 +1177,7 @@ int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, in
     if (e == cudaSuccess) e = cudaMalloc(&t->dY, sizeof(double) * (size_t)n_y * N);
     if (e == cudaSuccess) e = cudaMemcpy(t->dX, X, sizeof(double) * N * d, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(t->dY, Y, sizeof(double) * (size_t)n_y * N, cudaMemcpyHostToDevice);
-    const int nt = (N + 31) / 32;
+    const int nt = train_nt(N);
     t->ntri = nt * (nt + 1) / 2;
     t->Np = nt * 32;
     t->nwarps = std::max(2, std::min(nt, 16));          // one warp per unit of a panel (nt units)
@@ -1254,8 +1254,8 @@ static int trainer_launch(bi_trainer t, const double* theta, const int32_t* y_in
             cudaStreamSynchronize(s);
             const double nb = (double)P.B;
             std::fprintf(stderr, "[train timing] cycles per problem (thread 0): load %.0f  diag update %.0f  potrf+inv %.0f  wait updates %.0f  "
-                         "solves %.0f  z %.0f  alpha %.0f  Kinv %.0f\n", z[0] / nb, z[1] / nb, z[2] / nb, z[3] / nb,
-                         z[4] / nb, z[5] / nb, z[6] / nb, z[7] / nb);
+                         "solves %.0f  alpha %.0f  Kinv %.0f\n", z[0] / nb, z[1] / nb, z[2] / nb, z[3] / nb,
+                         z[4] / nb, z[5] / nb, z[7] / nb);
         }
 #endif
         TCK(cudaGetLastError());

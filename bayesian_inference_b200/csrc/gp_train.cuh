@@ -21,6 +21,9 @@
 // units (nt - j tiles of L, j tiles of M), one per warp; the diagonal tile is factorised by warp 0 with K4's blocked
 // potrf (8-column panels, DMMA trailing updates, 8 x 8 inverses) and the panel solve is K4's blocked triangular solve on
 // DMMA; M_jj = L_jj^-T is that same solve applied to the identity tile.
+// The targets ride inside the matrix as row N (the augmented-row device of K4): the factor of [[K, y], [y^T, 0]] has
+// z = L^-1 y as row N and -z.z as that row's would-be pivot (replaced by 1), so y.K^-1.y = z.z falls out of the last
+// potrf, and column N of M = L_aug^-T is -L^-T z = -alpha: no separate forward / backward substitution.
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
@@ -33,7 +36,7 @@
 namespace bi {
 
 constexpr int TRAIN_MAX_D = 16;       // length scales per kernel (parameters of the model)
-constexpr int TRAIN_MAX_NT = 31;      // N <= 992
+constexpr int TRAIN_MAX_NT = 31;      // N + 1 <= 992
 
 struct LmlParams {
     const double* X;        // (N, d) design, row-major
@@ -61,18 +64,20 @@ __device__ unsigned long long train_dbg[12];   // developer timing: cycles of th
 #endif
 
 __host__ __device__ __forceinline__ int tri_idx(int i, int j) { return i * (i + 1) / 2 + j; }
+// tiles per side: the N x N matrix plus one augmented row (the targets y, see gp_factor_kernel), padded to 32
+__host__ __device__ __forceinline__ int train_nt(int N) { return (N + 1 + 31) / 32; }
 
 __host__ inline size_t lml_tiles_doubles(int N) {        // per problem: lower tiles of K / L / K^-1
-    const int nt = (N + 31) / 32;
+    const int nt = train_nt(N);
     return (size_t)nt * (nt + 1) / 2 * 1024;
 }
 __host__ inline size_t lml_factor_smem_bytes(int N, int nwarps) {
-    const int nt = (N + 31) / 32, Np = nt * 32;
-    size_t dbl = 3 * (size_t)Np + 1024 + 256 + 32 + 32 * 33 + (size_t)nwarps + 8;
+    const int nt = train_nt(N), Np = nt * 32;
+    size_t dbl = (size_t)Np + 1024 + 256 + 32 + 32 * 33 + (size_t)nwarps + 8;
     return dbl * 8 + (size_t)nt * (nt + 1) / 2 * 2 * sizeof(int) + 16;
 }
 __host__ inline size_t lml_grad_smem_bytes(int N, int d) {
-    const int nt = (N + 31) / 32, Np = nt * 32;
+    const int nt = train_nt(N), Np = nt * 32;
     return ((size_t)((N * d + 1) & ~1) + Np + 32 * (TRAIN_MAX_D + 2) + TRAIN_MAX_D + 4) * 8 + (size_t)nt * (nt + 1) / 2 * 2 * sizeof(int) + 16;
 }
 
@@ -168,7 +173,7 @@ template <int KIND>
 __global__ void __launch_bounds__(256) gp_kbuild_kernel(const LmlParams P) {
     __shared__ double sInv[TRAIN_MAX_D];
     __shared__ double sXp[32 * TRAIN_MAX_D], sXq[32 * TRAIN_MAX_D];
-    const int N = P.N, d = P.d, nt = (N + 31) / 32, ntri = nt * (nt + 1) / 2;
+    const int N = P.N, d = P.d, nt = train_nt(N), ntri = nt * (nt + 1) / 2;
     const int tI = blockIdx.x, tid = threadIdx.x;
     const long long b = blockIdx.y;
     int ti = (int)((sqrt(8.0 * tI + 1.0) - 1.0) * 0.5);
@@ -187,6 +192,7 @@ __global__ void __launch_bounds__(256) gp_kbuild_kernel(const LmlParams P) {
     const double eta = P.has_white ? exp(th[d + (P.has_const ? 1 : 0)]) : 0.0;
     __syncthreads();
     double* T = P.Kt + ((size_t)b * ntri + tI) * 1024;
+    const double* y = P.Y + (size_t)(P.y_index ? P.y_index[b] : b) * N;
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
         const int e = tid + 256 * u, r = e >> 5, c = e & 31, p = ti * 32 + r, q = tj * 32 + c;
@@ -198,18 +204,21 @@ __global__ void __launch_bounds__(256) gp_kbuild_kernel(const LmlParams P) {
         double kv, gf;
         kernel_and_gfun<KIND>(sq, kv, gf);
         const double dg = (p == q) ? 1.0 : 0.0;
-        T[e] = (p < N && q < N) ? kv + cst + dg * (eta + P.alpha) : dg;
+        double val = (p < N && q < N) ? kv + cst + dg * (eta + P.alpha) : dg;
+        if (p == N || q == N) {                       // the augmented row / column: y, with a zero on the diagonal
+            const int o = (p == N) ? q : p;
+            val = (o < N) ? y[o] : 0.0;
+        }
+        T[e] = val;
     }
 }
 
 // ---- launch 2: factorisation, inverse factor, K^-1, alpha, LML.  One CTA per problem, persistent.
 __global__ void __launch_bounds__(512, 1) gp_factor_kernel(const LmlParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int N = P.N, nt = (N + 31) / 32, Np = nt * 32, ntri = nt * (nt + 1) / 2;
+    const int N = P.N, nt = train_nt(N), Np = nt * 32, ntri = nt * (nt + 1) / 2;
     const int tid = threadIdx.x, nth = blockDim.x, lane = tid & 31, warp = tid >> 5, NW = nth >> 5;
-    double* sY = reinterpret_cast<double*>(smem_raw);             // [Np] targets, zero padded
-    double* sZ = sY + Np;                                         // [Np] L^-1 y
-    double* sAl = sZ + Np;                                        // [Np] K^-1 y
+    double* sAl = reinterpret_cast<double*>(smem_raw);            // [Np] K^-1 y
     double* sLjj = sAl + Np;                                      // [1024] L_jj as B-operand fragments (blocked panel solve)
     double* sLinvB = sLjj + 1024;                                 // [256]  inverses of its four 8 x 8 diagonal blocks
     double* sRinv = sLinvB + 256;                                 // [32]   1 / L_kk
@@ -233,11 +242,7 @@ __global__ void __launch_bounds__(512, 1) gp_factor_kernel(const LmlParams P) {
         long long t0_ = clock64();
 #endif
         double* Lt = P.Kt + (size_t)b * ntri * 1024;              // lower tiles (i, j) at tri_idx(i, j)
-        {
-            const long long yrow = P.y_index ? P.y_index[b] : b;
-            for (int idx = tid; idx < Np; idx += nth) sY[idx] = idx < N ? P.Y[yrow * N + idx] : 0.0;
-            if (tid == 0) *sOk = 1;
-        }
+        if (tid == 0) *sOk = 1;
         __syncthreads();
         TR_T(0);
 
@@ -275,8 +280,10 @@ __global__ void __launch_bounds__(512, 1) gp_factor_kernel(const LmlParams P) {
 #pragma unroll
                     for (int c = 0; c < 32; ++c) sL[lane * 33 + c] = T[lane * 32 + c];
                     __syncwarp();
-                    double mypiv, quad;
-                    if (warp_potrf_blocked(sL, sLjj, sLinvB, sRinv, lane, mypiv, -1, quad) != 0 && lane == 0) *sOk = 0;
+                    double mypiv, quad = 0.0;
+                    const int aug = (j == nt - 1) ? N - j * 32 : -1;        // row N: the targets
+                    if (warp_potrf_blocked(sL, sLjj, sLinvB, sRinv, lane, mypiv, aug, quad) != 0 && lane == 0) *sOk = 0;
+                    if (aug >= 0 && lane == 0) sRed[0] = quad;              // z.z = y K^-1 y
                     __syncwarp();
 #pragma unroll
                     for (int c = 0; c < 32; ++c) T[lane * 32 + c] = (c <= lane) ? sL[lane * 33 + c] : 0.0;
@@ -332,38 +339,20 @@ __global__ void __launch_bounds__(512, 1) gp_factor_kernel(const LmlParams P) {
             TR_T(4);
         }
 
-        // ---- z = L^-1 y = M^T y   (thread = element of z)
-        for (int idx = tid; idx < Np; idx += nth) {
-            const int k = idx >> 5, c = idx & 31;
-            double s = 0.0;
-            for (int ip = 0; ip <= k; ++ip) {
-                const double* M = Mt + (size_t)tri_idx(k, ip) * 1024 + c;
-                const double* y = sY + ip * 32;
-#pragma unroll 8
-                for (int r = 0; r < 32; ++r) s = fma(M[r * 32], y[r], s);
+        // ---- alpha = -column N of M; then that column is cleared so that M M^T is K^-1 on the first N rows
+        {
+            const int ral = N - (nt - 1) * 32;
+            for (int idx = tid; idx < Np; idx += nth) {
+                double* m = Mt + (size_t)tri_idx(nt - 1, idx >> 5) * 1024 + (idx & 31) * 32 + ral;
+                const double a = (idx < N) ? -*m : 0.0;
+                sAl[idx] = a;
+                P.Ab[(size_t)b * Np + idx] = a;
+                if (idx != N) *m = 0.0;
             }
-            sZ[idx] = s;
         }
         __syncthreads();
         TR_T(5);
-        // ---- a = L^-T z = M z      (warp = row)
-        for (int row = warp; row < Np; row += NW) {
-            const int ip = row >> 5, r = row & 31;
-            double s = 0.0;
-            for (int k = ip; k < nt; ++k) s = fma(Mt[(size_t)tri_idx(k, ip) * 1024 + r * 32 + lane], sZ[k * 32 + lane], s);
-            s = warp_sum(s);
-            if (lane == 0) {
-                sAl[row] = s;
-                P.Ab[(size_t)b * Np + row] = s;
-            }
-        }
-        TR_T(6);
-        double qd = 0.0;
-        for (int idx = tid; idx < Np; idx += nth) qd = fma(sZ[idx], sZ[idx], qd);
-        qd = warp_sum(qd);
-        if (lane == 0) sRed[warp] = qd;
         if (P.L_out != nullptr) {       // the fitted state scikit-learn keeps (_gpr.py:335-366): L_, alpha_ and the LML
-            __syncthreads();
             double* Lo = P.L_out + (size_t)b * N * N;
             for (int e = tid; e < N * N; e += nth) {
                 const int p = e / N, q = e - p * N;
@@ -388,11 +377,8 @@ __global__ void __launch_bounds__(512, 1) gp_factor_kernel(const LmlParams P) {
             __syncthreads();
         }
         TR_T(7);
-        if (tid == 0) {
-            double s = 0.0;
-            for (int w = 0; w < NW; ++w) s += sRed[w];
-            P.lml[b] = *sOk ? (-0.5 * s - logdet - 0.5 * N * 1.8378770664093453) : -INFINITY;     // log(2 pi)
-        }
+        if (tid == 0)
+            P.lml[b] = *sOk ? (-0.5 * sRed[0] - logdet - 0.5 * N * 1.8378770664093453) : -INFINITY;     // log(2 pi)
     }
 }
 
@@ -401,7 +387,7 @@ __global__ void __launch_bounds__(512, 1) gp_factor_kernel(const LmlParams P) {
 template <int KIND, int DMAX>
 __global__ void __launch_bounds__(512, 2) gp_grad_kernel(const LmlParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int N = P.N, d = P.d, nt = (N + 31) / 32, Np = nt * 32, ntri = nt * (nt + 1) / 2;
+    const int N = P.N, d = P.d, nt = train_nt(N), Np = nt * 32, ntri = nt * (nt + 1) / 2;
     const int tid = threadIdx.x, nth = blockDim.x, lane = tid & 31, warp = tid >> 5, NW = nth >> 5;
     const long long b = blockIdx.x;
     double* sXs = reinterpret_cast<double*>(smem_raw);            // [N][d] design / length scale

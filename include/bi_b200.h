@@ -195,7 +195,7 @@ int bi_log_posterior_sets(bi_handle h, const double* theta, const int32_t* set_i
  * bi_trainer_factor: what fit() keeps for predict (_gpr.py:335-366): L_out (B, N, N) = chol(K + alpha I) lower,
  *                    alpha_out (B, N) = K^-1 y, lml_out (B).
  * The plain calls take DEVICE pointers and enqueue on `stream`; the _host calls take HOST pointers and synchronise.
- * N <= 992, d <= 16. */
+ * N <= 991, d <= 16. */
 typedef struct bi_trainer_s* bi_trainer;
 int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, int32_t n_y, int32_t kind,
                       int32_t has_const, int32_t has_white, double alpha, int32_t device, bi_trainer* out);
