@@ -262,11 +262,7 @@ __global__ void __launch_bounds__(GP_WT * 8, GP_WT == 32 ? 2 : 1) gp_predict_ker
         load_group(bcur, ftop - 4 * q, 0);
         while (q < ngroups) {
             const int f0 = ftop - 4 * q;
-#ifdef GP_EXP_NOK2
-            const int ngrp = 1;
-#else
             const int ngrp = (klim_of(f0) + 3) >> 2;
-#endif
             const int kl3 = klim_of(f0 - 3);       // the shortest fragment of the group
             double acc[2][4][2];
 #pragma unroll

@@ -277,7 +277,13 @@ def fit_gps(design, Y_pca_T, spec: KernelSpec, alpha: float, n_restarts: int = 0
     starts[:, 0] = spec.theta0
     if R > 1:
         starts[:, 1:] = rng.uniform(lo, hi, (P, R - 1, spec.n_hyper))
-    yidx = np.repeat(np.arange(P, dtype=np.int32), R)
+    # one process per GPU: the components are independent, so rank r fits the slice P_r and the results are gathered
+    # (no exchange on the data path); every rank draws the same starts, so the fit does not depend on the world size
+    rank, world = _dist_rank_world()
+    per = -(-P // world)
+    p0, p1 = min(P, rank * per), min(P, (rank + 1) * per)
+    Pl = p1 - p0
+    yidx = np.repeat(np.arange(p0, p1, dtype=np.int32), R)
     trainer = None
     if objective is None:
         trainer = DeviceGPTrainer(X, Y, spec, alpha, device)
@@ -291,18 +297,37 @@ def fit_gps(design, Y_pca_T, spec: KernelSpec, alpha: float, n_restarts: int = 0
         return -lml, -grad
 
     try:
-        xs, fs, _, nbatch = batched_lbfgsb(neg, starts.reshape(P * R, -1), lo, hi, maxiter=maxiter)
-        fs = np.where(np.isfinite(fs), fs, np.inf).reshape(P, R)
-        best = np.argmin(fs, axis=1)
-        theta = xs.reshape(P, R, -1)[np.arange(P), best]
-        if trainer is not None:
-            lml, L, al = trainer.factor(theta, np.arange(P, dtype=np.int32))
+        if Pl > 0:
+            xs, fs, _, nbatch = batched_lbfgsb(neg, starts[p0:p1].reshape(Pl * R, -1), lo, hi, maxiter=maxiter)
+            fs = np.where(np.isfinite(fs), fs, np.inf).reshape(Pl, R)
+            best = np.argmin(fs, axis=1)
+            theta = xs.reshape(Pl, R, -1)[np.arange(Pl), best]
+        else:
+            theta, fs, best, nbatch = np.empty((0, spec.n_hyper)), np.empty((0, R)), np.empty(0, int), 0
+        if trainer is not None and Pl > 0:
+            lml, L, al = trainer.factor(theta, np.arange(p0, p1, dtype=np.int32))
         else:                                      # host-logic tests: the caller's objective has no factor output
-            lml, L, al = -fs[np.arange(P), best], np.empty((P, 0, 0)), np.empty((P, 0))
+            lml, L, al = -fs[np.arange(Pl), best], np.empty((Pl, 0, 0)), np.empty((Pl, 0))
     finally:
         if trainer is not None:
             trainer.close()
+    if world > 1:
+        import torch.distributed as dist
+        parts: list[Any] = [None] * world
+        dist.all_gather_object(parts, (theta, lml, L, al, nbatch, nev))
+        theta, lml, L, al = (np.concatenate([p[i] for p in parts if len(p[0])], axis=0) for i in range(4))
+        nbatch, nev = max(p[4] for p in parts), sum(p[5] for p in parts)
     return FittedGPs(spec, X, theta, lml, L, al, n_batches=nbatch, n_evaluations=nev)
+
+
+def _dist_rank_world() -> tuple[int, int]:
+    try:
+        import torch.distributed as dist
+    except ImportError:          # torch is plumbing only; a single-process fit does not need it
+        return 0, 1
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
 
 
 def pca_transform(Y, n_pc: int, max_n_components: int | None = None):

@@ -110,3 +110,52 @@ def test_pca_transform_matches_sklearn():
     sgn = np.sign(np.sum(comps * pca.components_, axis=1))        # a principal axis is defined up to its sign
     assert np.allclose(comps * sgn[:, None], pca.components_, atol=1e-10)
     assert np.allclose(got * sgn[:6], want[:, :6], atol=1e-10)
+
+
+# ---- world_size-2 gloo: the components of a fit are sharded over the ranks and gathered ---------------------------------
+def _fit_worker(rank, world, port, q):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        z = np.load(GOLD)
+        kind, hc, hw, d = (int(v) for v in z["c0_meta"])
+        X, Y, al = z["c0_X"], z["c0_Y"], float(z["c0_alpha"])        # 3 components over 2 ranks: 2 + 1
+        spec = tr.KernelSpec(kind, d, bool(hc), bool(hw), z["c0_theta0"], z["c0_bounds"])
+        seen = []
+
+        def obj(th, yi):
+            seen.extend(np.unique(yi).tolist())
+            return gp_lml.log_marginal_likelihood_batch(X, Y, th, kind, hc, hw, al, yi)
+
+        fit = tr.fit_gps(X, Y, spec, al, n_restarts=3, seed=4, objective=obj)
+        q.put((rank, fit.theta, fit.lml, sorted(set(seen)), fit.n_evaluations))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_fit_is_sharded_by_component_gloo_world2():
+    import socket
+
+    import torch.multiprocessing as mp
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_fit_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    res = sorted([q.get(timeout=300) for _ in procs], key=lambda t: t[0])
+    [p.join(60) for p in procs]
+    z = np.load(GOLD)
+    kind, hc, hw, d = (int(v) for v in z["c0_meta"])
+    X, Y, al = z["c0_X"], z["c0_Y"], float(z["c0_alpha"])
+    spec = tr.KernelSpec(kind, d, bool(hc), bool(hw), z["c0_theta0"], z["c0_bounds"])
+    single = tr.fit_gps(X, Y, spec, al, n_restarts=3, seed=4,
+                        objective=lambda th, yi: gp_lml.log_marginal_likelihood_batch(X, Y, th, kind, hc, hw, al, yi))
+    for rank, theta, lml, seen, nev in res:
+        assert np.array_equal(theta, single.theta) and np.array_equal(lml, single.lml)     # same fit on every rank
+        assert seen == ([0, 1] if rank == 0 else [2])                                      # each rank fitted only its slice
+        assert nev == single.n_evaluations

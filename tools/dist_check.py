@@ -43,8 +43,25 @@ def main():
     assert ds.world == dist.get_world_size()
     ds.run_mcmc(a.theta, 50)
     assert np.array_equal(ds.get_chain(), ref.get_chain()), "device-resident sharded chain != single-GPU chain"
+    # emulator training: the principal components of a fit sharded over the ranks, results gathered
+    from bayesian_inference_b200 import training
+    rng = np.random.RandomState(1)
+    X = rng.uniform(0, 1, (96, 4))
+    Y = np.sin(X @ rng.normal(size=(4, 10)) * 2.0).T + 0.2 * rng.normal(size=(10, 96))
+    spec = training.kernel_spec({"matern": {"nu": 1.5, "length_scale_bounds_factor": [0.1, 10]},
+                                 "noise": {"args": {"noise_level": 0.25, "noise_level_bounds": [1e-4, 1]}}}, np.zeros(4), np.ones(4))
+    fit = training.fit_gps(X, Y, spec, 1e-10, n_restarts=4, seed=3, device=local)
+    with training.DeviceGPTrainer(X, Y, spec, 1e-10, device=local) as t:
+        lml_chk, _ = t.log_marginal_likelihood(fit.theta, np.arange(10, dtype=np.int32))
+    assert fit.theta.shape == (10, spec.n_hyper) and fit.L.shape == (10, 96, 96)
+    assert np.max(np.abs(lml_chk - fit.lml) / np.abs(fit.lml)) < 1e-12, "gathered fit is not what this rank evaluates"
+    chk = torch.tensor([float(np.sum(fit.theta))], device="cuda", dtype=torch.float64)
+    lst = [torch.empty_like(chk) for _ in range(dist.get_world_size())]
+    dist.all_gather(lst, chk)
+    assert all(float(t) == float(chk) for t in lst), "ranks hold different fits"
     if rank == 0:
-        print(f"dist_check ok: world={dist.get_world_size()} 100 walkers x 50 steps, acceptance {s.acceptance_fraction.mean():.3f}")
+        print(f"dist_check ok: world={dist.get_world_size()} 100 walkers x 50 steps, acceptance {s.acceptance_fraction.mean():.3f}; "
+              f"sharded GP fit of 10 components, lml sum {fit.lml.sum():.6f}")
     dev.close()
     dist.destroy_process_group()
 
