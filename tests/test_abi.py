@@ -48,6 +48,23 @@ def test_argument_errors_do_not_touch_the_gpu(lib):
     assert lib.bi_last_error(None) == b"null handle"
 
 
+def test_trainer_argument_errors_do_not_touch_the_gpu(lib):
+    import numpy as np
+    t = C.c_void_p()
+    X = np.zeros((8, 2))
+    Y = np.zeros((1, 8))
+    xp, yp = X.ctypes.data, Y.ctypes.data
+    assert lib.bi_trainer_create(None, 8, 2, yp, 1, 1, 0, 0, 1e-10, 0, C.byref(t)) == -1 and not t
+    assert lib.bi_trainer_create(xp, 8, 2, yp, 1, 7, 0, 0, 1e-10, 0, C.byref(t)) == -1          # unknown kernel kind
+    assert lib.bi_trainer_create(xp, 8, 17, yp, 1, 1, 0, 0, 1e-10, 0, C.byref(t)) == -1         # d > 16
+    assert lib.bi_trainer_create(xp, 992, 2, yp, 1, 1, 0, 0, 1e-10, 0, C.byref(t)) == -1        # N + 1 > 992
+    assert lib.bi_trainer_create(xp, 8, 2, yp, 1, 1, 0, 0, -1.0, 0, C.byref(t)) == -1           # negative jitter
+    assert lib.bi_trainer_lml_host(None, xp, None, 1, yp, yp) == -1
+    assert lib.bi_trainer_launches(None) == 0
+    lib.bi_trainer_destroy(None)
+    assert lib.bi_trainer_last_error(None) == b"null trainer"
+
+
 def test_struct_layout_matches_header():
     # 4 int32 + 12 pointers ; 6 int32 + 7 pointers + 2 int32
     assert C.sizeof(_lib.GroupDesc) == 16 + 12 * 8
