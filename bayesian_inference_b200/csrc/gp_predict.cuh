@@ -58,44 +58,56 @@ __host__ __device__ inline size_t gp_smem_bytes(int d, int Nmax, int GP_WT) {
 
 // ---- K1 arithmetic ------------------------------------------------------------------------------------------------
 // The CUDA math library's sqrt() / exp() cost ~150 issued instructions per kernel value here (slow-path branches,
-// BSSY/BSYNC pairs and two UMOVs per polynomial coefficient); K1 is issue bound, so both are restated branch-free
-// for the only argument range that occurs (sq >= 0 finite, exp of a non-positive number), with every constant an
-// operand from constant memory.  Accuracy: sqrt is correctly rounded up to the last Newton correction (<= 1 ulp),
-// exp(-x) <= 2 ulp for x <= 700 (degree-13 Taylor on |r| <= ln2/2: remainder 4e-18) -- far inside the 1e-13
-// relative tolerance of the kernel-vector parity test, and both agree with libm on the test fixtures to <= 4e-16.
-__constant__ double GP_EXP_C[16] = {
-    1.4426950408889634074,       // 0  log2(e)
-    6.93147180369123816490e-01,  // 1  ln2_hi
-    1.90821492927058770002e-10,  // 2  ln2_lo
-    6755399441055744.0,          // 3  1.5 * 2^52: adding it rounds to nearest integer and leaves it in the low word
-    1.0 / 6227020800.0,          // 4  1/13!
-    1.0 / 479001600.0,           // 5  1/12!
-    1.0 / 39916800.0,            // 6  1/11!
-    1.0 / 3628800.0,             // 7  1/10!
-    1.0 / 362880.0,              // 8  1/9!
-    1.0 / 40320.0,               // 9  1/8!
-    1.0 / 5040.0,                // 10 1/7!
-    1.0 / 720.0,                 // 11 1/6!
-    1.0 / 120.0,                 // 12 1/5!
-    1.0 / 24.0,                  // 13 1/4!
-    1.0 / 6.0,                   // 14 1/3!
-    700.0                        // 15 clamp: exp(-700) = 1e-304 is still a normal number
-};
+// BSSY/BSYNC pairs and two UMOVs per polynomial coefficient), and every FP64 instruction K1 issues competes with K2's
+// DMMAs for the one FP64 pipe of the SM sub-partition.  Both functions are restated branch-free for the only argument
+// range that occurs (sq >= 0 finite, exp of a non-positive number) with as few FP64 instructions as the accuracy allows:
+//   exp(-x) = 2^q * 2^(j/64) * e^r,  n = rint(-x 64 / ln2) = 64 q + j,  |r| <= ln2 / 128: a 64-entry table (one L1 load,
+//             off the FP64 pipe) and a degree-5 Taylor polynomial (remainder 3.4e-17) -- 12 FP64 instructions, <= 2 ulp;
+//   sqrt(s)  = MUFU.RSQ64H seed (2^-20) + two coupled Goldschmidt steps (2^-80: rounding limited, <= 2 ulp) -- 9.
+// Both agree with libm on the test fixtures to <= 4e-16 relative, far inside the 1e-13 tolerance of the kernel-vector
+// parity test.
+__constant__ double GP_EXP_C[12] = {
+    92.33248261689366,                   // 0  64 / ln2
+    6.93147180369123816490e-01 / 64.0,   // 1  ln2_hi / 64 (32 significant bits: n * hi is exact)
+    1.90821492927058770002e-10 / 64.0,   // 2  ln2_lo / 64
+    6755399441055744.0,                  // 3  1.5 * 2^52: adding it rounds to nearest integer and leaves it in the low word
+    1.0 / 120.0,                         // 4
+    1.0 / 24.0,                          // 5
+    1.0 / 6.0,                           // 6
+    700.0,                               // 7  clamp: exp(-700) = 1e-304 is still a normal number
+    0.0, 0.0, 0.0, 0.0};
+__device__ const double GP_EXP_T[64] = {   // 2^(j/64), correctly rounded
+    1.0, 1.0108892860517005, 1.0218971486541166, 1.0330248790212284,
+    1.0442737824274138, 1.0556451783605572, 1.0671404006768237, 1.0787607977571199,
+    1.0905077326652577, 1.102382583307841, 1.1143867425958924, 1.1265216186082418,
+    1.1387886347566916, 1.1511892299529827, 1.1637248587775775, 1.1763969916502812,
+    1.189207115002721, 1.202156731452703, 1.215247359980469, 1.22848053610687,
+    1.241857812073484, 1.255380757024691, 1.2690509571917332, 1.2828700160787783,
+    1.2968395546510096, 1.3109612115247644, 1.3252366431597413, 1.339667524053303,
+    1.3542555469368927, 1.3690024229745905, 1.383909881963832, 1.3989796725383112,
+    1.4142135623730951, 1.42961333839197, 1.4451808069770467, 1.460917794180647,
+    1.4768261459394993, 1.4929077282912648, 1.5091644275934228, 1.5255981507445384,
+    1.5422108254079407, 1.559004400237837, 1.5759808451078865, 1.593142151342267,
+    1.6104903319492543, 1.6280274218573478, 1.645755478153965, 1.6636765803267364,
+    1.681792830507429, 1.7001063537185235, 1.718619298122478, 1.7373338352737062,
+    1.7562521603732995, 1.7753764925265212, 1.7947090750031072, 1.8142521755003989,
+    1.8340080864093424, 1.8539791250833855, 1.8741676341103, 1.8945759815869656,
+    1.9152065613971474, 1.9360617934922943, 1.9571441241754002, 1.978456026387951};
 
 __device__ __forceinline__ double exp_neg(double x) {   // exp(-x), x >= 0
-    x = fmin(x, GP_EXP_C[15]);
+    x = fmin(x, GP_EXP_C[7]);
     const double tm = fma(x, -GP_EXP_C[0], GP_EXP_C[3]);
-    const double nf = tm - GP_EXP_C[3];                 // n = rint(-x log2 e) <= 0
+    const double nf = tm - GP_EXP_C[3];                 // n = rint(-x 64 / ln2) <= 0
     double r = fma(nf, -GP_EXP_C[1], -x);
-    r = fma(nf, -GP_EXP_C[2], r);                       // r = -x - n ln2, |r| <= ln2 / 2
-    double p = GP_EXP_C[4];
-#pragma unroll
-    for (int i = 5; i <= 14; ++i) p = fma(p, r, GP_EXP_C[i]);
+    r = fma(nf, -GP_EXP_C[2], r);                       // r = -x - n ln2 / 64, |r| <= ln2 / 128
+    const int n = __double2loint(tm);
+    const double tj = __ldg(GP_EXP_T + (n & 63));       // n = 64 q + j with j = n & 63, q = n >> 6 (floor)
+    double p = fma(GP_EXP_C[4], r, GP_EXP_C[5]);
+    p = fma(p, r, GP_EXP_C[6]);
     p = fma(p, r, 0.5);
     p = fma(p, r, 1.0);
     p = fma(p, r, 1.0);
-    const int n = __double2loint(tm);
-    return p * __hiloint2double((n + 1023) << 20, 0);   // n >= -1010: the scale is a normal power of two
+    return (tj * p) * __hiloint2double(((n >> 6) + 1023) << 20, 0);   // q >= -1010: the scale is a normal power of two
 }
 
 __device__ __forceinline__ double sqrt_pos(double s) {  // sqrt(s), s >= 0 finite; returns 1e-150 for s < 1e-300
@@ -107,9 +119,9 @@ __device__ __forceinline__ double sqrt_pos(double s) {  // sqrt(s), s >= 0 finit
     for (int it = 0; it < 2; ++it) {
         const double r = fma(-g, h, 0.5);
         g = fma(g, r, g);
-        h = fma(h, r, h);
+        if (it == 0) h = fma(h, r, h);
     }
-    return fma(fma(-g, g, s), h, g);                    // one Newton correction of the rounded result
+    return g;
 }
 
 template <int kind>
