@@ -24,7 +24,7 @@ EXPORTS = [
     "bi_kernel_vectors", "bi_kernel_vectors_host", "bi_predict_pc", "bi_predict_pc_host",
     "bi_predict_group", "bi_predict_group_host", "bi_predict", "bi_predict_host",
     "bi_log_posterior", "bi_log_posterior_host", "bi_loglikelihood_host",
-    "bi_stretch_propose", "bi_stretch_accept", "bi_set_data_sets", "bi_log_posterior_sets",
+    "bi_stretch_propose", "bi_stretch_accept", "bi_set_data_sets", "bi_log_posterior_sets", "bi_stretch_randoms_philox",
     "bi_trainer_create", "bi_trainer_lml", "bi_trainer_lml_host", "bi_trainer_factor", "bi_trainer_factor_host",
     "bi_trainer_destroy", "bi_trainer_last_error", "bi_trainer_launches",
 ]
@@ -145,7 +145,8 @@ def load() -> C.CDLL:
     lib.bi_trainer_last_error.restype = C.c_char_p
     lib.bi_trainer_launches.argtypes = [h]
     lib.bi_trainer_launches.restype = C.c_int64
-    for name in EXPORTS[8:28]:
+    lib.bi_stretch_randoms_philox.argtypes = [h, C.c_uint64, C.c_uint64, i32, i32, C.c_double, dp, dp, dp, dp, dp, C.c_void_p]
+    for name in EXPORTS[8:29]:
         getattr(lib, name).restype = C.c_int
     if lib.bi_abi_version() != 1:
         raise BackendUnavailable(f"ABI version mismatch: library {lib.bi_abi_version()}, package 1")

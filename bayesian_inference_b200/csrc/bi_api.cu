@@ -1061,6 +1061,20 @@ int bi_stretch_accept(bi_handle h, double* coords, double* logp, const int32_t* 
     return 0;
 }
 
+int bi_stretch_randoms_philox(bi_handle h, uint64_t seed, uint64_t step0, int32_t nsteps, int32_t n_half, double a,
+                              int32_t* s_idx, int32_t* c_idx, double* zz, double* factors, double* logu, void* stream) {
+    if (!h || !s_idx || !c_idx || !zz || !factors || !logu || nsteps < 0 || n_half < 1 || !(a > 1.0))
+        return fail(h, BI_E_ARG, "bad argument");
+    if (nsteps == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    const long long n = (long long)nsteps * 2 * n_half;
+    stretch_randoms_philox_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        seed, step0, nsteps, n_half, h->d, a, s_idx, c_idx, zz, factors, logu);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
 // ---- several experimental data sets on one emulator image (closure tests) --------------------------------
 int bi_set_data_sets(bi_handle h, int32_t n_sets, const double* y, const double* y_err) {
     if (!h || n_sets <= 0 || !y || !y_err) return fail(h, BI_E_ARG, "bad argument");

@@ -305,6 +305,18 @@ class DeviceEmulator:
                                                 C.c_void_p(n_accepted.data_ptr()), C.c_void_p(nan_flag.data_ptr()),
                                                 C.c_void_p(stream)), "bi_stretch_accept")
 
+    def stretch_randoms_philox(self, seed: int, step0: int, nsteps: int, n_half: int, a: float, out: dict) -> None:
+        """Fill out['s_idx'|'c_idx'|'zz'|'factors'|'logu'] (CUDA tensors (>= nsteps, 2, n_half)) for steps step0 ...
+        step0 + nsteps - 1 with counter-based random numbers generated on the device (bi_stretch_randoms_philox)."""
+        import torch
+
+        stream = torch.cuda.current_stream(out["zz"].device).cuda_stream
+        self._check(self._lib.bi_stretch_randoms_philox(
+            self._h, C.c_uint64(seed & 0xFFFFFFFFFFFFFFFF), C.c_uint64(step0), int(nsteps), int(n_half), float(a),
+            C.c_void_p(out["s_idx"].data_ptr()), C.c_void_p(out["c_idx"].data_ptr()), C.c_void_p(out["zz"].data_ptr()),
+            C.c_void_p(out["factors"].data_ptr()), C.c_void_p(out["logu"].data_ptr()), C.c_void_p(stream)),
+            "bi_stretch_randoms_philox")
+
 
 def from_analysis(emulation_config, emulation_results, *, min, max, experimental_results=None, sigma_exp=None,
                   device: int = 0, max_batch: int = 0) -> DeviceEmulator:

@@ -281,6 +281,111 @@ class DeviceStretchEnsemble(StretchEnsemble):
                 done += nb
 
 
+class DevicePhiloxEnsemble(DeviceStretchEnsemble):
+    """Device-resident stretch move whose random numbers are generated on the GPU as well (the variant
+    "reported separately"): counter-based Philox4x32-10 keyed by ``seed`` (``bi_stretch_randoms_philox``), fixed
+    even / odd halves instead of emcee's per-step permutation.  Nothing crosses the PCIe bus inside a block of steps, so
+    a block is a fixed launch sequence on fixed buffers and can be replayed as ONE CUDA graph (``graph=True``; single
+    process only) -- the launch-bound regime of small ensembles (100 walkers, F = 200: ~25 us kernels).
+
+    The chain is a valid stretch-move chain but NOT emcee's for the same seed; it is reproducible from (seed, step) and
+    independent of the block size and of ``graph``.
+    """
+
+    def __init__(self, nwalkers: int, ndim: int, device_emulator, mode: str = "dense", a: float = 2.0, seed: int = 0,
+                 block: int = 64, group=None, graph: bool = False):
+        super().__init__(nwalkers, ndim, device_emulator, mode=mode, a=a, seed=0, block=block, group=group)
+        if nwalkers % 2:
+            raise ValueError("the fixed even / odd split needs an even number of walkers")
+        self.seed, self.graph, self._step = int(seed), bool(graph), 0
+        self.n_graph_replays = 0
+
+    def _fill_randoms(self, step0: int, nb: int, rd: dict) -> None:
+        self.dev.stretch_randoms_philox(self.seed, step0, nb, self.nwalkers // 2, self.a, rd)
+
+    def sample(self, initial_state: np.ndarray, iterations: int = 1, log_prob0: Optional[np.ndarray] = None):
+        import torch
+
+        x0 = np.array(initial_state, dtype=np.float64, copy=True)
+        W, nd, ns, B = self.nwalkers, self.ndim, self.nwalkers // 2, self.block
+        if x0.shape != (W, nd):
+            raise ValueError("incompatible input dimensions")
+        if np.linalg.cond(np.cov(x0, rowvar=False).reshape(nd, nd)) > 1e8:
+            raise ValueError("Initial state has a large condition number. Make sure that your walkers are linearly independent.")
+        device = torch.device("cuda", self.dev.device)
+        with torch.cuda.device(device):
+            f64 = dict(dtype=torch.float64, device=device)
+            coords = torch.from_numpy(x0).to(device)
+            logp = torch.empty(W, **f64)
+            per = (W + self.world - 1) // self.world
+            self._send = torch.full((per,), float("nan"), **f64)
+            self._recv = torch.empty(per * self.world, **f64)
+            if log_prob0 is None:
+                self._device_log_prob(coords, logp)
+            else:
+                logp.copy_(torch.from_numpy(np.array(log_prob0, dtype=np.float64)))
+            if bool(torch.isnan(logp).any()):
+                raise ValueError("Probability function returned NaN")
+            q = torch.empty((ns, nd), **f64)
+            new_lp = torch.empty(ns, **f64)
+            n_acc = torch.zeros(W, dtype=torch.int64, device=device)
+            nan_flag = torch.zeros(1, dtype=torch.int32, device=device)
+            rd = {k: torch.empty((B, 2, ns), dtype=torch.int32, device=device) for k in ("s_idx", "c_idx")}
+            rd.update({k: torch.empty((B, 2, ns), **f64) for k in ("zz", "factors", "logu")})
+            chain_b = torch.empty((B, W, nd), **f64)
+            lp_b = torch.empty((B, W), **f64)
+
+            def run_block(nb: int) -> None:
+                for t in range(nb):
+                    for split in range(2):
+                        s_idx = rd["s_idx"][t, split]
+                        self.dev.stretch_propose(coords, s_idx, rd["c_idx"][t, split], rd["zz"][t, split], q)
+                        self._device_log_prob(q, new_lp)
+                        self.dev.stretch_accept(coords, logp, s_idx, q, new_lp, rd["factors"][t, split], rd["logu"][t, split],
+                                                n_acc, nan_flag)
+                    chain_b[t].copy_(coords)
+                    lp_b[t].copy_(logp)
+
+            graph = None
+            if self.graph and self.world == 1 and iterations >= B:
+                # every kernel of the block has run once (module loading is not capturable): a throw-away half-step on copies
+                self._fill_randoms(self._step, 1, rd)
+                c2, l2, a2 = coords.clone(), logp.clone(), n_acc.clone()
+                self.dev.stretch_propose(c2, rd["s_idx"][0, 0], rd["c_idx"][0, 0], rd["zz"][0, 0], q)
+                self._device_log_prob(q, new_lp)
+                self.dev.stretch_accept(c2, l2, rd["s_idx"][0, 0], q, new_lp, rd["factors"][0, 0], rd["logu"][0, 0], a2, nan_flag)
+                nan_flag.zero_()
+                torch.cuda.synchronize(device)
+                calls, rows = self.n_log_prob_calls, self.n_log_prob_rows
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    run_block(B)
+                self.n_log_prob_calls, self.n_log_prob_rows = calls - 1, rows - ns      # capture and warm-up evaluate nothing kept
+            done = 0
+            while done < iterations:
+                nb = min(B, iterations - done)
+                self._fill_randoms(self._step, nb, rd)
+                if graph is not None and nb == B:
+                    graph.replay()
+                    self.n_graph_replays += 1
+                    self.n_log_prob_calls += 2 * nb
+                    self.n_log_prob_rows += 2 * nb * ns
+                else:
+                    run_block(nb)
+                chain_h, lp_h = chain_b[:nb].cpu().numpy(), lp_b[:nb].cpu().numpy()      # synchronises: the block is done
+                if int(nan_flag.item()):
+                    raise ValueError("Probability function returned NaN")
+                self._accepted += n_acc.cpu().numpy()
+                n_acc.zero_()
+                self._step += nb
+                for t in range(nb):
+                    self.iteration += 1
+                    self._chain.append(chain_h[t])
+                    self._log_prob.append(lp_h[t])
+                    yield chain_h[t], lp_h[t]
+                done += nb
+
+
 class BatchedClosureEnsemble:
     """Several independent ensembles advanced in lock-step on one GPU, chain c against experimental data set c
     (SURVEY §8 f3).  The reference runs its closure tests -- one MCMC per validation design point, each against that

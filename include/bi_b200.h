@@ -167,6 +167,14 @@ int bi_stretch_accept(bi_handle h, double* coords, double* logp, const int32_t* 
                       const double* new_lp, const double* factors, const double* logu, int64_t ns,
                       int64_t* n_accepted, int32_t* nan_flag, void* stream);
 
+/* bi_stretch_randoms_philox: the chain-independent numbers of `nsteps` steps generated ON the device (Philox4x32-10,
+ * counter = (proposal, half, step), key = seed), shaped (nsteps, 2, n_half) like the host-drawn arrays the two calls
+ * above consume: s_idx / c_idx (int32), zz, factors = (d - 1) log zz, logu.  Step `step0 + t` always yields the same
+ * numbers whatever the block size.  The ensemble is split into even / odd walkers (fixed halves), so this is not
+ * emcee's stream: the chain is a valid stretch-move chain but differs from the reference's for the same seed. */
+int bi_stretch_randoms_philox(bi_handle h, uint64_t seed, uint64_t step0, int32_t nsteps, int32_t n_half, double a,
+                              int32_t* s_idx, int32_t* c_idx, double* zz, double* factors, double* logu, void* stream);
+
 /* ---- several experimental data sets on one emulator image (closure tests, steer_analysis.py:168-183) ----------------
  * The reference validates an analysis by running one MCMC per validation design point, each against that point's
  * pseudo-data (data_IO.py:362-372) and the SAME emulators, one after the other.  Here the pseudo-data sets are loaded

@@ -174,3 +174,22 @@ def test_predrawn_randoms_reproduce_the_sampler_stream():
             lp[si[acc]] = nl[acc]
         chain.append(coords.copy())
     assert np.array_equal(np.array(chain), s.get_chain())
+
+
+def test_philox_restatement_known_answer_vectors():
+    """oracle/philox.py against the Random123 known-answer vectors for philox4x32-10 (zero, all-ones, digits of pi)."""
+    from oracle import philox as ph
+
+    def run(c, k):
+        return [int(v) for v in ph.philox4x32_10(*[np.uint64(x) for x in c], *[np.uint64(x) for x in k])]
+
+    assert run([0, 0, 0, 0], [0, 0]) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert run([0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert run([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+    r = ph.stretch_randoms(seed=5, step0=3, nsteps=4, nwalkers=12, ndim=3)
+    assert r["zz"].shape == (4, 2, 6) and np.all((r["zz"] >= 0.5) & (r["zz"] <= 2.0)) and np.all(r["logu"] < 0)
+    assert np.array_equal(r["s_idx"][0, 0], np.arange(0, 12, 2)) and np.array_equal(r["s_idx"][0, 1], np.arange(1, 12, 2))
+    assert np.all(r["c_idx"][:, 0] % 2 == 1) and np.all(r["c_idx"][:, 1] % 2 == 0)      # partners from the other half
+    later = ph.stretch_randoms(seed=5, step0=5, nsteps=2, nwalkers=12, ndim=3)          # a step does not depend on the block
+    assert all(np.array_equal(later[k], r[k][2:]) for k in r)

@@ -81,3 +81,77 @@ def test_device_sampler_raises_on_nan_like_emcee():
         s = DeviceStretchEnsemble(16, d, dev, seed=5)
         with pytest.raises(ValueError, match="returned NaN"):
             s.run_mcmc(x0, 5)
+
+
+def test_philox_randoms_match_numpy_restatement():
+    """bi_stretch_randoms_philox == oracle/philox.py: indices and zz bit for bit, the logarithms to 2 ulp."""
+    import torch
+
+    from bayesian_inference_b200.device import DeviceEmulator
+    from oracle import philox as ph
+
+    z, _ = load_golden("mid")
+    d, W, nb = int(z["d"]), 48, 7
+    with DeviceEmulator(image.EmulatorImage.from_flat(z)) as dev:
+        rd = {k: torch.empty((nb, 2, W // 2), dtype=torch.int32, device="cuda") for k in ("s_idx", "c_idx")}
+        rd.update({k: torch.empty((nb, 2, W // 2), dtype=torch.float64, device="cuda") for k in ("zz", "factors", "logu")})
+        dev.stretch_randoms_philox(0x1234567890ABCDEF, (1 << 32) - 3, nb, W // 2, 2.0, rd)       # the step counter crosses 2^32
+        got = {k: v.cpu().numpy() for k, v in rd.items()}
+    want = ph.stretch_randoms(0x1234567890ABCDEF, (1 << 32) - 3, nb, W, d, 2.0)
+    for k in ("s_idx", "c_idx", "zz"):
+        assert np.array_equal(got[k], want[k]), k
+    for k in ("factors", "logu"):
+        assert np.max(np.abs(got[k] - want[k]) / np.maximum(np.abs(want[k]), 1e-300)) < 5e-16, k
+
+
+def test_philox_sampler_is_the_host_replay_and_graph_invariant():
+    """DevicePhiloxEnsemble == the pre-drawn device sampler fed with the numpy-restated random numbers (same chain bit
+    for bit), whatever the block size, and identical when the blocks are replayed as CUDA graphs."""
+    import torch
+
+    from bayesian_inference_b200.device import DeviceEmulator
+    from bayesian_inference_b200.ensemble import DevicePhiloxEnsemble
+    from oracle import philox as ph
+
+    z, _ = load_golden("mid")
+    W, nsteps, seed, d = 32, 300, 99, int(z["d"])
+    x0 = np.random.RandomState(3).uniform(0.1, 0.9, (W, d))
+
+    class Replay(DevicePhiloxEnsemble):
+        def _fill_randoms(self, step0, nb, rd):
+            r = ph.stretch_randoms(self.seed, step0, nb, self.nwalkers, self.ndim, self.a)
+            for k, v in r.items():
+                rd[k][:nb].copy_(torch.from_numpy(v))
+
+    with DeviceEmulator(image.EmulatorImage.from_flat(z)) as dev:
+        a = DevicePhiloxEnsemble(W, d, dev, seed=seed, block=64)
+        a.run_mcmc(x0, nsteps)
+        b = Replay(W, d, dev, seed=seed, block=50)
+        b.run_mcmc(x0, nsteps)
+        g = DevicePhiloxEnsemble(W, d, dev, seed=seed, block=64, graph=True)
+        g.run_mcmc(x0, 200)
+        g.run_mcmc(g.get_chain()[-1], 100, log_prob0=g.get_log_prob()[-1])      # the step counter carries on
+    assert np.array_equal(a.get_chain(), b.get_chain()) and np.array_equal(a.get_log_prob(), b.get_log_prob())
+    assert np.array_equal(a.acceptance_fraction, b.acceptance_fraction)
+    assert g.n_graph_replays == 4 and np.array_equal(g.get_chain(), a.get_chain())
+    assert g.n_log_prob_rows == a.n_log_prob_rows              # warm-up and capture are not counted as evaluations
+    assert 0.15 < a.acceptance_fraction.mean() < 0.85
+
+
+def test_philox_sampler_samples_the_same_posterior():
+    """Not emcee's stream, but the same target: posterior means of the Philox chain and of the RandomState chain agree
+    within a fraction of the posterior width (32 walkers x 800 steps, first 200 dropped)."""
+    from bayesian_inference_b200.device import DeviceEmulator
+    from bayesian_inference_b200.ensemble import DevicePhiloxEnsemble, DeviceStretchEnsemble
+
+    z, _ = load_golden("mid")
+    W, d = 32, int(z["d"])
+    x0 = np.random.RandomState(3).uniform(0.2, 0.8, (W, d))
+    with DeviceEmulator(image.EmulatorImage.from_flat(z)) as dev:
+        p = DevicePhiloxEnsemble(W, d, dev, seed=1, block=100, graph=True)
+        p.run_mcmc(x0, 800)
+        r = DeviceStretchEnsemble(W, d, dev, seed=1, block=100)
+        r.run_mcmc(x0, 800)
+    cp, cr = p.get_chain()[200:].reshape(-1, d), r.get_chain()[200:].reshape(-1, d)
+    assert np.all(np.abs(cp.mean(0) - cr.mean(0)) < 0.35 * cr.std(0))
+    assert np.all(np.abs(cp.std(0) / cr.std(0) - 1.0) < 0.35)
