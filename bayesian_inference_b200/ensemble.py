@@ -299,6 +299,12 @@ class DevicePhiloxEnsemble(DeviceStretchEnsemble):
             raise ValueError("the fixed even / odd split needs an even number of walkers")
         self.seed, self.graph, self._step = int(seed), bool(graph), 0
         self.n_graph_replays = 0
+        self._buf = None           # state, scratch and (with graph=True) the captured block live as long as the sampler
+
+    def reset(self) -> None:
+        """Forget the chain and restart the random stream at step 0; buffers and the captured graph are kept."""
+        super().reset()
+        self._step = 0
 
     def _fill_randoms(self, step0: int, nb: int, rd: dict) -> None:
         self.dev.stretch_randoms_philox(self.seed, step0, nb, self.nwalkers // 2, self.a, rd)
@@ -315,25 +321,28 @@ class DevicePhiloxEnsemble(DeviceStretchEnsemble):
         device = torch.device("cuda", self.dev.device)
         with torch.cuda.device(device):
             f64 = dict(dtype=torch.float64, device=device)
-            coords = torch.from_numpy(x0).to(device)
-            logp = torch.empty(W, **f64)
-            per = (W + self.world - 1) // self.world
-            self._send = torch.full((per,), float("nan"), **f64)
-            self._recv = torch.empty(per * self.world, **f64)
+            if self._buf is None:
+                per = (W + self.world - 1) // self.world
+                self._send = torch.full((per,), float("nan"), **f64)
+                self._recv = torch.empty(per * self.world, **f64)
+                rd = {k: torch.empty((B, 2, ns), dtype=torch.int32, device=device) for k in ("s_idx", "c_idx")}
+                rd.update({k: torch.empty((B, 2, ns), **f64) for k in ("zz", "factors", "logu")})
+                self._buf = dict(coords=torch.empty((W, nd), **f64), logp=torch.empty(W, **f64), q=torch.empty((ns, nd), **f64),
+                                 new_lp=torch.empty(ns, **f64), n_acc=torch.zeros(W, dtype=torch.int64, device=device),
+                                 nan_flag=torch.zeros(1, dtype=torch.int32, device=device), rd=rd,
+                                 chain_b=torch.empty((B, W, nd), **f64), lp_b=torch.empty((B, W), **f64), graph=None)
+            bf = self._buf
+            coords, logp, q, new_lp, n_acc, nan_flag = (bf[k] for k in ("coords", "logp", "q", "new_lp", "n_acc", "nan_flag"))
+            rd, chain_b, lp_b = bf["rd"], bf["chain_b"], bf["lp_b"]
+            coords.copy_(torch.from_numpy(x0))
+            n_acc.zero_()
+            nan_flag.zero_()
             if log_prob0 is None:
                 self._device_log_prob(coords, logp)
             else:
                 logp.copy_(torch.from_numpy(np.array(log_prob0, dtype=np.float64)))
             if bool(torch.isnan(logp).any()):
                 raise ValueError("Probability function returned NaN")
-            q = torch.empty((ns, nd), **f64)
-            new_lp = torch.empty(ns, **f64)
-            n_acc = torch.zeros(W, dtype=torch.int64, device=device)
-            nan_flag = torch.zeros(1, dtype=torch.int32, device=device)
-            rd = {k: torch.empty((B, 2, ns), dtype=torch.int32, device=device) for k in ("s_idx", "c_idx")}
-            rd.update({k: torch.empty((B, 2, ns), **f64) for k in ("zz", "factors", "logu")})
-            chain_b = torch.empty((B, W, nd), **f64)
-            lp_b = torch.empty((B, W), **f64)
 
             def run_block(nb: int) -> None:
                 for t in range(nb):
@@ -346,8 +355,7 @@ class DevicePhiloxEnsemble(DeviceStretchEnsemble):
                     chain_b[t].copy_(coords)
                     lp_b[t].copy_(logp)
 
-            graph = None
-            if self.graph and self.world == 1 and iterations >= B:
+            if self.graph and self.world == 1 and iterations >= B and bf["graph"] is None:
                 # every kernel of the block has run once (module loading is not capturable): a throw-away half-step on copies
                 self._fill_randoms(self._step, 1, rd)
                 c2, l2, a2 = coords.clone(), logp.clone(), n_acc.clone()
@@ -357,10 +365,11 @@ class DevicePhiloxEnsemble(DeviceStretchEnsemble):
                 nan_flag.zero_()
                 torch.cuda.synchronize(device)
                 calls, rows = self.n_log_prob_calls, self.n_log_prob_rows
-                graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph):
+                bf["graph"] = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(bf["graph"]):
                     run_block(B)
                 self.n_log_prob_calls, self.n_log_prob_rows = calls - 1, rows - ns      # capture and warm-up evaluate nothing kept
+            graph = bf["graph"]
             done = 0
             while done < iterations:
                 nb = min(B, iterations - done)

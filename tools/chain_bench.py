@@ -26,7 +26,7 @@ def main():
 
     from bayesian_inference_b200 import image, synthetic
     from bayesian_inference_b200.device import DeviceEmulator
-    from bayesian_inference_b200.ensemble import DeviceStretchEnsemble, StretchEnsemble
+    from bayesian_inference_b200.ensemble import DevicePhiloxEnsemble, DeviceStretchEnsemble, StretchEnsemble
 
     spec = synthetic.config(a.workload)
     if a.walkers:
@@ -39,16 +39,21 @@ def main():
     out = {"workload": spec.name, "walkers": W, "steps": a.steps, "mode": a.mode, "n_obs": img.n_features}
     with DeviceEmulator(img, max_batch=max(W, a.closures * W)) as dev:
         for name, mk in (("host", lambda: StretchEnsemble(W, d, lambda X: dev.log_posterior(X, n_div=1.0, mode=a.mode), seed=3)),
-                         ("device", lambda: DeviceStretchEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block))):
+                         ("device", lambda: DeviceStretchEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block)),
+                         ("device_philox", lambda: DevicePhiloxEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block)),
+                         ("device_philox_graph", lambda: DevicePhiloxEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block, graph=True))):
             s = mk()
-            s.run_mcmc(x0, 10)             # warm-up
-            s = mk()
+            s.run_mcmc(x0, max(10, a.block) if "graph" in name else 10)      # warm-up (captures the block graph)
+            if "graph" in name:
+                s.reset()                  # keeps buffers and the captured graph: steady-state replay is what is timed
+            else:
+                s = mk()
             torch.cuda.synchronize()
             t0 = time.perf_counter()
             s.run_mcmc(x0, a.steps)
             torch.cuda.synchronize()
             dt = time.perf_counter() - t0
-            out[name] = {"seconds": dt, "steps_per_s": a.steps / dt, "evals_per_s": s.n_log_prob_rows / dt,
+            out[name] = {"seconds": dt, "steps_per_s": a.steps / dt, "evals_per_s": (a.steps + 1) * W / dt,
                          "acceptance": float(s.acceptance_fraction.mean())}
             out[name + "_chain_sum"] = float(np.sum(s.get_chain()))
         if a.closures:
@@ -70,6 +75,7 @@ def main():
                                        "evals_per_s": ens.n_log_prob_rows / dt,
                                        "speedup_vs_serial_device_chains": (C_ * a.steps / dt) / out["device"]["steps_per_s"]}
     out["identical_chain"] = out.pop("host_chain_sum") == out.pop("device_chain_sum")
+    out["identical_chain_philox_graph"] = out.pop("device_philox_chain_sum") == out.pop("device_philox_graph_chain_sum")
     print(json.dumps(out))
 
 
