@@ -301,10 +301,12 @@ class DevicePhiloxEnsemble(DeviceStretchEnsemble):
         self.n_graph_replays = 0
         self._buf = None           # state, scratch and (with graph=True) the captured block live as long as the sampler
 
-    def reset(self) -> None:
-        """Forget the chain and restart the random stream at step 0; buffers and the captured graph are kept."""
+    def reset(self, rewind: bool = False) -> None:
+        """Forget the chain; buffers and the captured graph are kept.  The random stream carries on (burn-in and
+        production of ``mcmc.run_mcmc`` must not see the same numbers) unless ``rewind`` restarts it at step 0."""
         super().reset()
-        self._step = 0
+        if rewind:
+            self._step = 0
 
     def _fill_randoms(self, step0: int, nb: int, rd: dict) -> None:
         self.dev.stretch_randoms_philox(self.seed, step0, nb, self.nwalkers // 2, self.a, rd)

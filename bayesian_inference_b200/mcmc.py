@@ -89,13 +89,17 @@ def run_mcmc(config, closure_index: int = -1, *, emulation_config=None, emulatio
     rng = np.random.RandomState(seed)
     if sampler == "device":
         sampler = DeviceStretchEnsemble(config.n_walkers, ndim, log_posterior.device(), mode=mode, random_state=rng)
+    elif sampler in ("device_philox", "device_philox_graph"):      # device-side random numbers: not emcee's stream
+        from .ensemble import DevicePhiloxEnsemble
+        sampler = DevicePhiloxEnsemble(config.n_walkers, ndim, log_posterior.device(), mode=mode,
+                                       seed=int(rng.randint(0, 2**31 - 1)), graph=sampler.endswith("graph"))
     elif sampler == "host":
         fn = log_posterior.log_posterior_walkers
         if distributed:
             fn = ShardedLogProb(fn)
         sampler = StretchEnsemble(config.n_walkers, ndim, fn, random_state=rng)
     else:
-        raise ValueError("sampler must be 'device' or 'host'")
+        raise ValueError("sampler must be 'device', 'host', 'device_philox' or 'device_philox_graph'")
 
     logger.info("Initializing sampler...")
     random_pos = rng.uniform(lo, hi, (config.n_walkers, ndim))                       # mcmc.py:88

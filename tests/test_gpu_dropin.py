@@ -80,6 +80,14 @@ def test_run_mcmc_device_and_host_samplers_agree(toy, tmp_path):
     assert np.array_equal(a["chain"], b["chain"]) and np.array_equal(a["log_prob"], b["log_prob"])
     assert np.array_equal(a["acceptance_fraction"], b["acceptance_fraction"])
     assert np.all(np.isfinite(a["log_prob"])) and a["n_log_prob_rows"] == b["n_log_prob_rows"]
+    # device-side random numbers (not emcee's stream): reproducible, graph replay changes nothing, burn-in and production
+    # do not reuse random numbers
+    cfg.n_burn_steps, cfg.n_sampling_steps = 80, 130
+    p1 = mcmc.run_mcmc(cfg, sampler="device_philox", **kw)
+    p2 = mcmc.run_mcmc(cfg, sampler="device_philox_graph", **kw)
+    assert p1["chain"].shape == (130, 16, d) and np.array_equal(p1["chain"], p2["chain"])
+    assert not np.array_equal(p1["chain"][:60], a["chain"]) and np.all(np.isfinite(p1["log_prob"]))
+    assert 0.1 < p1["acceptance_fraction"].mean() < 0.9
     lp.close()
     emulation.clear_cache()
 

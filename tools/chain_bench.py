@@ -45,7 +45,7 @@ def main():
             s = mk()
             s.run_mcmc(x0, max(10, a.block) if "graph" in name else 10)      # warm-up (captures the block graph)
             if "graph" in name:
-                s.reset()                  # keeps buffers and the captured graph: steady-state replay is what is timed
+                s.reset(rewind=True)       # keeps buffers and the captured graph: steady-state replay is what is timed
             else:
                 s = mk()
             torch.cuda.synchronize()
