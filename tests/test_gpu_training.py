@@ -117,3 +117,30 @@ def test_trained_group_drives_the_log_posterior():
         mw, sw = g.predict(theta, return_std=True)
         assert np.max(np.abs(m[:, p] - mw)) < 1e-8 * max(1.0, np.max(np.abs(mw)))
         assert np.max(np.abs(v[:, p] - sw ** 2)) < 1e-8 * max(1.0, np.max(sw ** 2))
+
+
+def test_objective_is_deterministic_and_batch_independent():
+    """The same hyper-parameter vector gives bit-identical results on every call, alone or inside any batch, in any
+    slot of the persistent grid (a data race or a stale scratch tile would show up here)."""
+    rng = np.random.RandomState(11)
+    N, d = 150, 5
+    X = rng.uniform(0, 1, (N, d))
+    Y = np.sin(X @ rng.normal(size=(d, 3)) * 2.0).T + 0.2 * rng.normal(size=(3, N))
+    spec = tr.kernel_spec({"matern": {"nu": 2.5, "length_scale_bounds_factor": [0.1, 10]},
+                           "constant": {"constant_value": 1.0, "constant_value_bounds": [1e-3, 10]},
+                           "noise": {"args": {"noise_level": 0.25, "noise_level_bounds": [1e-4, 1]}}}, np.zeros(d), np.ones(d))
+    B = 700                                                    # more than two waves of the 296 resident CTAs
+    theta = rng.uniform(spec.bounds[:, 0], spec.bounds[:, 1], (B, spec.n_hyper))
+    yidx = rng.randint(0, 3, B).astype(np.int32)
+    with tr.DeviceGPTrainer(X, Y, spec, 1e-10) as t:
+        l1, g1 = t.log_marginal_likelihood(theta, yidx)
+        l2, g2 = t.log_marginal_likelihood(theta, yidx)
+        perm = rng.permutation(B)
+        l3, g3 = t.log_marginal_likelihood(theta[perm], yidx[perm])
+        l4, g4 = t.log_marginal_likelihood(theta[:5], yidx[:5])
+        f1 = t.factor(theta[:9], yidx[:9])
+        f2 = t.factor(theta[:9][::-1].copy(), yidx[:9][::-1].copy())
+    assert np.array_equal(l1, l2) and np.array_equal(g1, g2)
+    assert np.array_equal(l1[perm], l3) and np.array_equal(g1[perm], g3)
+    assert np.array_equal(l1[:5], l4) and np.array_equal(g1[:5], g4)
+    assert all(np.array_equal(a, b[::-1]) for a, b in zip(f1, f2))
