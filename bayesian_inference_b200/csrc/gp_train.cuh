@@ -193,16 +193,17 @@ __global__ void __launch_bounds__(256) gp_kbuild_kernel(const LmlParams P) {
     __syncthreads();
     double* T = P.Kt + ((size_t)b * ntri + tI) * 1024;
     const double* y = P.Y + (size_t)(P.y_index ? P.y_index[b] : b) * N;
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    auto element = [&](int u, bool live) {
         const int e = tid + 256 * u, r = e >> 5, c = e & 31, p = ti * 32 + r, q = tj * 32 + c;
-        double sq = 0.0;
-        for (int m = 0; m < d; ++m) {
-            const double df = sXp[r * d + m] - sXq[m * 32 + c];
-            sq = fma(df, df, sq);
+        double kv = 0.0, gf;
+        if (live) {
+            double sq = 0.0;
+            for (int m = 0; m < d; ++m) {
+                const double df = sXp[r * d + m] - sXq[m * 32 + c];
+                sq = fma(df, df, sq);
+            }
+            kernel_and_gfun<KIND>(sq, kv, gf);
         }
-        double kv, gf;
-        kernel_and_gfun<KIND>(sq, kv, gf);
         const double dg = (p == q) ? 1.0 : 0.0;
         double val = (p < N && q < N) ? kv + cst + dg * (eta + P.alpha) : dg;
         if (p == N || q == N) {                       // the augmented row / column: y, with a zero on the diagonal
@@ -210,6 +211,13 @@ __global__ void __launch_bounds__(256) gp_kbuild_kernel(const LmlParams P) {
             val = (o < N) ? y[o] : 0.0;
         }
         T[e] = val;
+    };
+    if (ti < nt - 1) {                                // four independent sqrt / exp chains per thread
+#pragma unroll
+        for (int u = 0; u < 4; ++u) element(u, true);
+    } else {                                          // last tile row: rows past N are padding (warp-uniform test)
+#pragma unroll
+        for (int u = 0; u < 4; ++u) element(u, ti * 32 + (tid >> 5) + 8 * u < N);
     }
 }
 
