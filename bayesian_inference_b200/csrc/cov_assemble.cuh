@@ -78,6 +78,16 @@ __global__ void __launch_bounds__(256, 2) cov_assemble_kernel(const CovParams P)
         if (!overlap) {
             // structurally zero tile and its mirror: plain zero fill, one 256-byte row segment per 16 lanes
             const int rr = lane >> 4, cc = (lane & 15) * 2;
+            if ((P.Fo & 1) == 0) {             // even row length: every (row, even column) pair is 16-byte aligned
+                const double2 z2 = make_double2(0.0, 0.0);
+#pragma unroll 4
+                for (int r = rr; r < 32; r += 2) {
+                    const int row = i0 + r, mcol = i0 + cc;          // jt < it here: j0 + cc + 1 < Fo and j0 + r < Fo always
+                    if (row < P.Fo) *reinterpret_cast<double2*>(out + (long long)row * P.Fo + j0 + cc) = z2;
+                    if (mcol < P.Fo) *reinterpret_cast<double2*>(out + (long long)(j0 + r) * P.Fo + mcol) = z2;
+                }
+                continue;
+            }
 #pragma unroll 4
             for (int r = rr; r < 32; r += 2) {
                 const int row = i0 + r, col = j0 + cc;           // jt < it here, so col + 1 < Fo always
