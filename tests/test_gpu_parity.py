@@ -249,3 +249,37 @@ def test_not_positive_definite_reports_pivot_and_nan():
     with _dev(z) as dev:
         got, info = dev.loglikelihood(np.ones((2, F)), cov, return_info=True)
     assert np.isfinite(got[0]) and np.isnan(got[1]) and info[0] == 0 and info[1] == 37
+
+
+# ---- analytic known-answer tests on the CUDA path itself: answers known in closed form, no oracle -------
+def test_kat_cuda_path_closed_form_answers():
+    from test_oracle_golden import _tiny_image
+
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    # (1) theta = a design point with eta -> 0: the GP mean reproduces its training targets, the variance collapses
+    z, yv = _tiny_image()
+    with DeviceEmulator(image.EmulatorImage.from_flat(z)) as dev:
+        m, v = dev.predict_pc(z["g0_X"])
+    assert np.max(np.abs(m - yv.T)) < 1e-4 and np.max(v) < 1e-5
+    # (2) P = Q (nothing truncated) and S square orthonormal: cov = s^2 S^T diag(v) S has eigenvalues s^2 v
+    z, _ = _tiny_image(P=3, F=3)
+    th = np.array([[0.3, 0.6]])
+    with DeviceEmulator(image.EmulatorImage.from_flat(z)) as dev:
+        m, v = dev.predict_pc(th)
+        _, cov = dev.predict(th, n_div=1.0)
+    assert np.allclose(np.sort(np.linalg.eigvalsh(cov[0])), np.sort(4.0 * v[0]), rtol=1e-11, atol=1e-18)
+    # (3) one-bin observables: the merged covariance is diagonal and the likelihood is a sum of 1-d Gaussians
+    z, _ = _tiny_image(P=2, F=3)
+    z["blocks"] = np.array([[0, 0, 0, 1], [0, 1, 1, 1], [0, 2, 2, 1]])
+    th = np.array([[0.2, 0.7], [0.8, 0.1], [1.2, 0.5]])          # the last row is outside the prior box
+    with DeviceEmulator(image.EmulatorImage.from_flat(z)) as dev:
+        mean, cov = dev.predict(th[:2], n_div=1.0)
+        lps = {mode: dev.log_posterior(th, n_div=1.0, mode=mode) for mode in ("dense", "structured", "woodbury")}
+    for mode, lp in lps.items():
+        assert lp[2] == -np.inf, mode
+        for i in range(2):
+            c = np.diag(cov[i]) + z["y_err"] ** 2
+            assert np.count_nonzero(cov[i] - np.diag(np.diag(cov[i]))) == 0
+            want = -0.5 * np.sum((mean[i] - z["y"]) ** 2 / c) - 0.5 * np.sum(np.log(c))
+            assert abs(lp[i] - want) < 1e-11 * abs(want), (mode, lp[i], want)
