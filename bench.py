@@ -145,6 +145,10 @@ def time_cpu(img, theta, target_s: float, cores: int):
         t0 = time.perf_counter()
         out = pool.map(_cpu_eval, rows, chunksize=max(1, n // (cores * 8)))
         dt = time.perf_counter() - t0
+        k = int(max(4, min(n, 1.5 * rate / cores)))                                       # ~1.5 s on one worker: the per-core rate
+        t1 = time.perf_counter()
+        pool.map(_cpu_eval, rows[:k], chunksize=k)                                        # a single chunk runs on a single process
+        time_cpu.single_core = k / (time.perf_counter() - t1)
         return n / dt, n, dt, np.asarray(out)
     finally:
         pool.close()
@@ -339,6 +343,7 @@ def main() -> None:
             line["cpu_baseline"] = {"value": val, "unit": "evals/s", "cores": cores, "kind": "port",
                                     "sample": f"{n} evaluations cycling through the step's {W} walker rows, {dt:.1f} s, one "
                                               "single-threaded process per core, one theta per task",
+                                    "single_core_value": getattr(time_cpu, "single_core", None),
                                     "max_rel_diff_vs_gpu": float(np.max(np.abs(cpu_out[:m] - gpu_out) / np.abs(cpu_out[:m])))}
         else:
             line["cpu_baseline"] = None
