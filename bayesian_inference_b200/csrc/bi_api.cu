@@ -1133,7 +1133,7 @@ int bi_log_posterior_sets(bi_handle h, const double* theta, const int32_t* set_i
 struct bi_trainer_s {
     int device = 0, N = 0, d = 0, n_y = 0, kind = 0, has_const = 0, has_white = 0, nh = 0, sms = 0, nwarps = 0, occ = 1;
     double alpha = 0.0;
-    double *dX = nullptr, *dY = nullptr, *dScratch = nullptr, *dKt = nullptr, *dAb = nullptr;
+    double *dX = nullptr, *dY = nullptr, *dScratch = nullptr, *dKt = nullptr, *dGt = nullptr, *dAb = nullptr;
     size_t smem_factor = 0, smem_grad = 0, slot = 0, tiles = 0;
     long long cap = 0, chunk_max = 0;      // problems the K / alpha buffers hold now; upper limit per launch group
     int nslots = 0, ntri = 0, Np = 0;
@@ -1204,7 +1204,7 @@ int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, in
     t->slot = t->tiles;                                  // M = L^-T has as many tiles as the lower triangle
     t->nslots = t->sms * t->occ;
     // the K / K^-1 tiles of a launch group live in HBM: at most ~4 GB of them at a time
-    t->chunk_max = std::max<long long>(t->nslots, (long long)((4ull << 30) / (t->tiles * sizeof(double))));
+    t->chunk_max = std::max<long long>(t->nslots, (long long)((3ull << 30) / (t->tiles * sizeof(double))));     // x2: K and G tiles
     if (e == cudaSuccess && t->smem_factor > 48 * 1024)
         e = cudaFuncSetAttribute(gp_factor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_factor);
     if (e == cudaSuccess) e = kind == 0 ? trainer_attrs<0>(t) : kind == 1 ? trainer_attrs<1>(t) : kind == 2 ? trainer_attrs<2>(t) : trainer_attrs<3>(t);
@@ -1222,7 +1222,7 @@ int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, in
 void bi_trainer_destroy(bi_trainer t) {
     if (!t) return;
     cudaSetDevice(t->device);
-    cudaFree(t->dX); cudaFree(t->dY); cudaFree(t->dScratch); cudaFree(t->dKt); cudaFree(t->dAb);
+    cudaFree(t->dX); cudaFree(t->dY); cudaFree(t->dScratch); cudaFree(t->dKt); cudaFree(t->dGt); cudaFree(t->dAb);
     delete t;
 }
 
@@ -1234,10 +1234,11 @@ static int trainer_launch(bi_trainer t, const double* theta, const int32_t* y_in
     const long long need = std::min<long long>(B, t->chunk_max);
     if (need > t->cap) {                               // grow the K / alpha buffers (stream-ordered free of the old ones)
         TCK(cudaStreamSynchronize(s));
-        cudaFree(t->dKt); cudaFree(t->dAb);
-        t->dKt = t->dAb = nullptr;
+        cudaFree(t->dKt); cudaFree(t->dGt); cudaFree(t->dAb);
+        t->dKt = t->dGt = t->dAb = nullptr;
         t->cap = 0;
         TCK(cudaMalloc(&t->dKt, sizeof(double) * t->tiles * need));
+        TCK(cudaMalloc(&t->dGt, sizeof(double) * t->tiles * need));
         TCK(cudaMalloc(&t->dAb, sizeof(double) * (size_t)t->Np * need));
         t->cap = need;
     }
@@ -1247,7 +1248,7 @@ static int trainer_launch(bi_trainer t, const double* theta, const int32_t* y_in
         P.X = t->dX; P.Y = t->dY; P.y_index = y_index ? y_index + b0 : nullptr; P.theta = theta + b0 * t->nh;
         if (!y_index) P.Y = t->dY + b0 * t->N;         // problem b uses row b
         P.N = t->N; P.d = t->d; P.nh = t->nh; P.has_const = t->has_const; P.has_white = t->has_white;
-        P.alpha = t->alpha; P.Kt = t->dKt; P.Ab = t->dAb; P.scratch = t->dScratch; P.scratch_stride = (long long)t->slot;
+        P.alpha = t->alpha; P.Kt = t->dKt; P.Gt = grad ? t->dGt : nullptr; P.Ab = t->dAb; P.scratch = t->dScratch; P.scratch_stride = (long long)t->slot;
         P.lml = lml + b0; P.grad = grad ? grad + b0 * t->nh : nullptr;
         P.L_out = L_out ? L_out + (size_t)b0 * t->N * t->N : nullptr;
         P.alpha_out = alpha_out ? alpha_out + (size_t)b0 * t->N : nullptr;

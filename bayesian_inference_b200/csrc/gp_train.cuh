@@ -47,6 +47,8 @@ struct LmlParams {
     int N, d, nh, has_const, has_white;
     double alpha;
     double* Kt;             // (B, ntri, 1024) lower tiles: K + alpha I in, L during the factorisation, K^-1 out
+    double* Gt;             // (B, ntri, 1024) or nullptr: d(kernel)/d(log ell_m) / D_m per entry, written by the build for the
+                            // gradient launch (which then needs no sqrt / exp); nullptr when no gradient is asked for
     double* Ab;             // (B, Np) K^-1 y
     double* scratch;        // gridDim.x slots of scratch_stride doubles: the tiles of M = L^-T
     long long scratch_stride;
@@ -193,9 +195,10 @@ __global__ void __launch_bounds__(256) gp_kbuild_kernel(const LmlParams P) {
     __syncthreads();
     double* T = P.Kt + ((size_t)b * ntri + tI) * 1024;
     const double* y = P.Y + (size_t)(P.y_index ? P.y_index[b] : b) * N;
+    double* G = P.Gt ? P.Gt + ((size_t)b * ntri + tI) * 1024 : nullptr;
     auto element = [&](int u, bool live) {
         const int e = tid + 256 * u, r = e >> 5, c = e & 31, p = ti * 32 + r, q = tj * 32 + c;
-        double kv = 0.0, gf;
+        double kv = 0.0, gf = 0.0;
         if (live) {
             double sq = 0.0;
             for (int m = 0; m < d; ++m) {
@@ -211,6 +214,7 @@ __global__ void __launch_bounds__(256) gp_kbuild_kernel(const LmlParams P) {
             val = (o < N) ? y[o] : 0.0;
         }
         T[e] = val;
+        if (G != nullptr) G[e] = gf;
     };
     if (ti < nt - 1) {                                // four independent sqrt / exp chains per thread
 #pragma unroll
@@ -422,7 +426,8 @@ __global__ void __launch_bounds__(512, 2) gp_grad_kernel(const LmlParams P) {
         const double ap = sAl[p];
         const double* xp = sXs + p * d;
         const double* Krow = Kinv + (size_t)tri_idx(p >> 5, 0) * 1024 + (p & 31) * 32;
-#pragma unroll 2
+        const double* Grow = P.Gt + ((size_t)b * ntri + tri_idx(p >> 5, 0)) * 1024 + (p & 31) * 32;
+#pragma unroll 4
         for (int q0 = 0; q0 <= p; q0 += 32) {
             const int q = q0 + lane, qc = min(q, p);
             const double wv = fma(ap, sAl[qc], -Krow[(size_t)(q0 >> 5) * 1024 + (qc & 31)]);
@@ -431,14 +436,7 @@ __global__ void __launch_bounds__(512, 2) gp_grad_kernel(const LmlParams P) {
             gw += wd;
             gc += wd + w2;
             const double* xq = sXs + qc * d;
-            double sq = 0.0;
-            for (int m = 0; m < d; ++m) {
-                const double df = xp[m] - xq[m];
-                sq = fma(df, df, sq);
-            }
-            double kv, gf;
-            kernel_and_gfun<KIND>(sq, kv, gf);
-            const double wg = w2 * gf;
+            const double wg = w2 * Grow[(size_t)(q0 >> 5) * 1024 + (qc & 31)];      // gfun(sq) from the build launch
 #pragma unroll
             for (int m = 0; m < DMAX; ++m)
                 if (m < d) {
