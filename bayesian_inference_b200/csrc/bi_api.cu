@@ -1138,6 +1138,10 @@ struct bi_trainer_s {
     long long cap = 0, chunk_max = 0;      // problems the K / alpha buffers hold now; upper limit per launch group
     int nslots = 0, ntri = 0, Np = 0;
     long long launches = 0;
+    // staging buffers of the _host calls (theta, y_index, lml, grad), grown on demand and kept: a fit makes ~1e3 calls
+    double *hTh = nullptr, *hLml = nullptr, *hGrad = nullptr;
+    int32_t* hIdx = nullptr;
+    long long hcap = 0;
     std::string err;
 };
 
@@ -1223,6 +1227,7 @@ void bi_trainer_destroy(bi_trainer t) {
     if (!t) return;
     cudaSetDevice(t->device);
     cudaFree(t->dX); cudaFree(t->dY); cudaFree(t->dScratch); cudaFree(t->dKt); cudaFree(t->dGt); cudaFree(t->dAb);
+    cudaFree(t->hTh); cudaFree(t->hLml); cudaFree(t->hGrad); cudaFree(t->hIdx);
     delete t;
 }
 
@@ -1306,25 +1311,33 @@ static int trainer_host(bi_trainer t, const double* theta, const int32_t* y_inde
     if (B == 0) return 0;
     TCK(cudaSetDevice(t->device));
     const size_t NN = (size_t)t->N * t->N;
-    double *dTh = nullptr, *dLml = nullptr, *dGrad = nullptr, *dL = nullptr, *dAl = nullptr;
-    int32_t* dIdx = nullptr;
+    if (B > t->hcap) {
+        cudaFree(t->hTh); cudaFree(t->hLml); cudaFree(t->hGrad); cudaFree(t->hIdx);
+        t->hTh = t->hLml = t->hGrad = nullptr;
+        t->hIdx = nullptr;
+        t->hcap = 0;
+        const long long cap = std::max<long long>(B, 256);
+        TCK(cudaMalloc(&t->hTh, sizeof(double) * cap * t->nh));
+        TCK(cudaMalloc(&t->hLml, sizeof(double) * cap));
+        TCK(cudaMalloc(&t->hGrad, sizeof(double) * cap * t->nh));
+        TCK(cudaMalloc(&t->hIdx, sizeof(int32_t) * cap));
+        t->hcap = cap;
+    }
+    double *dTh = t->hTh, *dLml = t->hLml, *dGrad = grad_out ? t->hGrad : nullptr, *dL = nullptr, *dAl = nullptr;
+    int32_t* dIdx = y_index ? t->hIdx : nullptr;
     int rc = 0;
-    cudaError_t e = cudaMalloc(&dTh, sizeof(double) * B * t->nh);
-    if (e == cudaSuccess) e = cudaMalloc(&dLml, sizeof(double) * B);
-    if (e == cudaSuccess && grad_out) e = cudaMalloc(&dGrad, sizeof(double) * B * t->nh);
-    if (e == cudaSuccess && L_out) e = cudaMalloc(&dL, sizeof(double) * B * NN);
+    cudaError_t e = cudaSuccess;
+    if (L_out) e = cudaMalloc(&dL, sizeof(double) * B * NN);
     if (e == cudaSuccess && L_out) e = cudaMalloc(&dAl, sizeof(double) * B * t->N);
-    if (e == cudaSuccess && y_index) e = cudaMalloc(&dIdx, sizeof(int32_t) * B);
     if (e == cudaSuccess) e = cudaMemcpy(dTh, theta, sizeof(double) * B * t->nh, cudaMemcpyHostToDevice);
     if (e == cudaSuccess && y_index) e = cudaMemcpy(dIdx, y_index, sizeof(int32_t) * B, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) rc = trainer_launch(t, dTh, dIdx, B, dLml, dGrad, dL, dAl, nullptr);
-    if (e == cudaSuccess && rc == 0) e = cudaDeviceSynchronize();
-    if (e == cudaSuccess && rc == 0) e = cudaMemcpy(lml_out, dLml, sizeof(double) * B, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && rc == 0) e = cudaMemcpy(lml_out, dLml, sizeof(double) * B, cudaMemcpyDeviceToHost);     // default stream: ordered after the kernels
     if (e == cudaSuccess && rc == 0 && grad_out) e = cudaMemcpy(grad_out, dGrad, sizeof(double) * B * t->nh, cudaMemcpyDeviceToHost);
     if (e == cudaSuccess && rc == 0 && L_out) e = cudaMemcpy(L_out, dL, sizeof(double) * B * NN, cudaMemcpyDeviceToHost);
     if (e == cudaSuccess && rc == 0 && L_out) e = cudaMemcpy(alpha_out, dAl, sizeof(double) * B * t->N, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) rc = tfail(t, (int)e, std::string("bi_trainer host call: ") + cudaGetErrorString(e));
-    cudaFree(dTh); cudaFree(dLml); cudaFree(dGrad); cudaFree(dL); cudaFree(dAl); cudaFree(dIdx);
+    cudaFree(dL); cudaFree(dAl);
     return rc;
 }
 
