@@ -45,7 +45,8 @@ __global__ void __launch_bounds__(256) mean_kernel(const CovParams P) {
 // grid (ceil(Fo/32), W), 256 threads = 8 warps.  CTA (i, w) produces row tile i of walker w's covariance and, by
 // symmetry of T diag(v) T^T, the mirrored column tile: warp q takes the tiles j = q, q + 8, ... <= i, contracts
 // (T_i diag(v)) T_j^T on the FP64 tensor pipe (DMMA m8n8k4, operand fragments read straight from the row-major,
-// L1/L2-resident T) and writes tile (i, j) and its transpose (j, i), each with its own U entries.  Tiles whose
+// L1/L2-resident T) on top of U_ij / n_div and writes tile (i, j) and, with the same values, its transpose (j, i) -- the
+// reference's U = S_u diag(ev) S_u^T is symmetric up to the rounding of its own matrix product, ~1e-16.  Tiles whose
 // observables do not overlap (block-diagonal-per-observable merge, emulation.py:346-406) skip the contraction and
 // write zeros.  Half the flops of the full product, so the kernel is bound by its 8 F^2 bytes of HBM writes.
 __global__ void __launch_bounds__(256, 2) cov_assemble_kernel(const CovParams P) {
@@ -70,10 +71,6 @@ __global__ void __launch_bounds__(256, 2) cov_assemble_kernel(const CovParams P)
     for (int jt = warp; jt <= it; jt += 8) {
         const int j0 = jt * 32;
         double acc[4][4][2];
-#pragma unroll
-        for (int mf = 0; mf < 4; ++mf)
-#pragma unroll
-            for (int nf = 0; nf < 4; ++nf) acc[mf][nf][0] = acc[mf][nf][1] = 0.0;
         const bool overlap = P.tile_omax ? (P.tile_omax[jt] >= omin_i) : true;
         if (!overlap) {
             // structurally zero tile and its mirror: plain zero fill, one 256-byte row segment per 16 lanes
@@ -103,6 +100,28 @@ __global__ void __launch_bounds__(256, 2) cov_assemble_kernel(const CovParams P)
         }
         // operands: A = rows of T_i scaled by v (shared by the 8 warps: staged once in shared memory, fragment-major),
         // B = rows of T_j read straight from the row-major, L1/L2-resident T (row index clamped, never predicated)
+        // The accumulators start from U / n_div: the 16 loads are in flight together while the first operands arrive
+        // (one L2 round trip per tile; as an epilogue they cost four dependent round trips: 2.40 -> 1.35 ms on one dense
+        // 600-bin block).  Rows / columns past Fo are clamped (never stored).
+        {
+            const bool even = (P.Fo & 1) == 0;
+#pragma unroll
+            for (int mf = 0; mf < 4; ++mf) {
+                const double* Ur = P.Uc + (long long)min(i0 + mf * 8 + g, P.Fo - 1) * P.Fo;
+#pragma unroll
+                for (int nf = 0; nf < 4; ++nf) {
+                    const int col = j0 + nf * 8 + 2 * t;
+                    if (even) {
+                        const double2 uu = __ldcg(reinterpret_cast<const double2*>(Ur + min(col, P.Fo - 2)));
+                        acc[mf][nf][0] = uu.x * rinv;
+                        acc[mf][nf][1] = uu.y * rinv;
+                    } else {
+                        acc[mf][nf][0] = __ldcg(Ur + min(col, P.Fo - 1)) * rinv;
+                        acc[mf][nf][1] = __ldcg(Ur + min(col + 1, P.Fo - 1)) * rinv;
+                    }
+                }
+            }
+        }
         {
             int rb[4];
 #pragma unroll
@@ -130,7 +149,6 @@ __global__ void __launch_bounds__(256, 2) cov_assemble_kernel(const CovParams P)
             const int row = i0 + mf * 8 + g;
             if (row >= P.Fo) continue;
             const int orow = P.obs ? P.obs[row] : 0;
-            const double* Ur = P.Uc + (long long)row * P.Fo;
             double* po = out + (long long)row * P.Fo;
 #pragma unroll
             for (int nf = 0; nf < 4; ++nf) {
@@ -138,28 +156,17 @@ __global__ void __launch_bounds__(256, 2) cov_assemble_kernel(const CovParams P)
                 if (col >= P.Fo) continue;
                 const bool two = col + 1 < P.Fo;
                 const bool s0 = ocol[nf][0] == orow, s1 = two && ocol[nf][1] == orow;
-                double u0 = 0.0, u1 = 0.0;
-                if (two && even) {
-                    const double2 uu = __ldg(reinterpret_cast<const double2*>(Ur + col));   // row * Fo + col even: aligned
-                    u0 = uu.x;
-                    u1 = uu.y;
-                } else {
-                    u0 = __ldg(Ur + col);
-                    if (two) u1 = __ldg(Ur + col + 1);
-                }
-                const double o0 = s0 ? fma(u0, rinv, acc[mf][nf][0]) : 0.0;
-                const double o1 = s1 ? fma(u1, rinv, acc[mf][nf][1]) : 0.0;
+                const double o0 = s0 ? acc[mf][nf][0] : 0.0;
+                const double o1 = s1 ? acc[mf][nf][1] : 0.0;
                 if (two && even) {
                     *reinterpret_cast<double2*>(po + col) = make_double2(o0, o1);
                 } else {
                     po[col] = o0;
                     if (two) po[col + 1] = o1;
                 }
-                if (jt < it) {                                                   // mirrored tile (j, i), its own U entries
-                    out[(long long)col * P.Fo + row] = s0 ? fma(__ldg(P.Uc + (long long)col * P.Fo + row), rinv, acc[mf][nf][0]) : 0.0;
-                    if (two)
-                        out[(long long)(col + 1) * P.Fo + row] =
-                            s1 ? fma(__ldg(P.Uc + (long long)(col + 1) * P.Fo + row), rinv, acc[mf][nf][1]) : 0.0;
+                if (jt < it) {                                                   // mirrored tile (j, i): the same values
+                    out[(long long)col * P.Fo + row] = o0;
+                    if (two) out[(long long)(col + 1) * P.Fo + row] = o1;
                 }
             }
         }

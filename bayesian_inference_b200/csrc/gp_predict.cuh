@@ -51,8 +51,8 @@ __host__ __device__ inline size_t gp_smem_bytes(int d, int Nmax, int GP_WT) {
     b += sizeof(double) * (size_t)GP_WT * 4 * nks;   // sA  (32 walkers x 4*nks), operand-fragment-major
     b += sizeof(double) * (size_t)d * Nmax;          // sX
     b += sizeof(double) * (size_t)GP_WT * d;         // sTh
-    b += sizeof(double) * GP_WT * 4;                 // sSq  [wn][row]
-    b += sizeof(double) * GP_WT * 4;                 // sMn  [wn][row]
+    b += sizeof(double) * GP_WT * 8;                 // sSq  [wn][row] (up to 8 owners)
+    b += sizeof(double) * GP_WT * 8;                 // sMn  [wn][row]
     return b;
 }
 
@@ -143,8 +143,8 @@ __device__ __forceinline__ double stationary_kernel(double sq) {
 // so that four independent sqrt/exp dependency chains interleave.
 template <bool DO_GP, int KIND>
 __device__ __forceinline__ void gp_k1_loop(double* sA, const double* sX, const double* sTh, const PcDesc& pc, int d, int nks,
-                                           long long w0, long long W, double* __restrict__ k_out, int k_npc) {
-    const int tid = threadIdx.x, N = pc.N;
+                                           long long w0, long long W, double* __restrict__ k_out, int k_npc, int tid) {
+    const int N = pc.N;
     const int wl = tid >> 3, jl = tid & 7;
     const double* th = sTh + wl * d;
     double* krow = (k_out != nullptr && w0 + wl < W) ? k_out + ((w0 + wl) * k_npc + pc.local) * N : nullptr;
@@ -177,6 +177,168 @@ __device__ __forceinline__ void gp_k1_loop(double* sA, const double* sX, const d
     }
 }
 
+// K2 for one (walker tile, PC): the calling warps (8 per 32 walkers) contract the kernel vectors in sA with L^-1 and leave
+// their partial sums of squares and means in sSq / sMn ([owner][walker]).
+//
+// Warp tile = (8 MI walker rows) x (NF fragments of 8 rows of L^-1), MI = 8 / NF: 16 accumulator doubles either way.
+// NF = 2 (MI = 4, eight fragment owners per 32 walkers) is the default: every B fragment is loaded by exactly one warp of
+// the CTA and the B double buffer is 32 registers instead of 64 -- with NF = 4 the loop ran out of its 128 registers
+// (spills and re-materialised shared-memory addresses inside the k loop: ncu source page, profiles/r01_notes.md).
+#ifndef GP_K2_NF
+#define GP_K2_NF 2
+#endif
+constexpr int GP_K2_OWNERS = 16 / GP_K2_NF;   // fragment-group owners per 32 walkers = rows of sSq / sMn
+
+template <int GP_WT>
+__device__ __forceinline__ void gp_k2_tile(const PcDesc& pc, const double* sA, int warp, int lane, double* sSq, double* sMn) {
+    constexpr int NF = GP_K2_NF, MI = 8 / NF, NO = GP_K2_OWNERS;
+    constexpr int WM = GP_WT / (8 * MI);    // warps along the walker rows
+    const int N = pc.N, nks = pc.nks;
+    // warp (wm, wn): walker rows wm*8*MI.., fragment groups {q : snake(q) == wn}.  The B operand is cut into n-fragments
+    // of 8 rows of L^-1 (fragment f = rows 8f .. 8f+7; row N holds alpha).  Fragment f only needs the k-steps
+    // 0 .. min(ceil(N/4), 2f+2) - 1 (L^-1 is lower triangular) and fragments past row N do not exist, so the fragments
+    // are grouped NF at a time from the TOP (group 0 = the longest) and the groups dealt to the owners in snake order:
+    // every owner gets the same number of DMMAs to within a few per cent.  B (L2 resident, shared by every CTA of this
+    // PC) is streamed global -> registers in groups of 4 k-steps, one group ahead of the DMMAs that consume it.
+    const int wm = warp % WM;
+    const int wn = warp / WM;   // fragment-group owner 0 .. NO-1
+    const int g = lane >> 2, t = lane & 3;
+    double sumsq[MI], meanv[MI];
+#pragma unroll
+    for (int mi = 0; mi < MI; ++mi) sumsq[mi] = meanv[mi] = 0.0;
+    const double* sAw = sA + (size_t)(MI * wm) * nks * 32 + lane;
+    const double* Bl = pc.LinvF + lane;
+    const int kfull = (N + 3) >> 2;
+    const int ftop = N >> 3;                        // fragment holding row N
+    const int ngroups = (ftop + NF) / NF;
+
+    auto group_of = [&](int idx) {   // idx-th fragment group owned by this warp
+        const int blk = idx >> 1;
+        return blk * 2 * NO + ((idx & 1) ? 2 * NO - 1 - wn : wn);
+    };
+    auto klim_of = [&](int f) { return f < 0 ? 0 : min(kfull, 2 * f + 2); };
+    // loads are never predicated: past a fragment's triangle the packed operand holds zeros (4*grp+3 < nks always),
+    // and the fragments a bottom group lacks are clamped to fragment 0 and never multiplied
+    auto load_group = [&](double (&bb)[4][NF], int f0, int grp) {
+#pragma unroll
+        for (int nf = 0; nf < NF; ++nf) {
+            const double* bp = Bl + ((size_t)max(f0 - nf, 0) * nks + 4 * grp) * 32;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) bb[kk][nf] = __ldg(bp + kk * 32);
+        }
+    };
+
+    int idx = 0;
+    int q = group_of(0);
+    if (q < ngroups) {
+        double bcur[4][NF], bnxt[4][NF];
+        load_group(bcur, ftop - NF * q, 0);
+        while (q < ngroups) {
+            const int f0 = ftop - NF * q;
+            const int ngrp = (klim_of(f0) + 3) >> 2;
+            const int kl_last = klim_of(f0 - (NF - 1));       // the shortest fragment of the group
+            double acc[MI][NF][2];
+#pragma unroll
+            for (int mi = 0; mi < MI; ++mi)
+#pragma unroll
+                for (int nf = 0; nf < NF; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
+            const int next_q = group_of(idx + 1);
+            for (int grp = 0; grp < ngrp; ++grp) {
+                // prefetch the next group of k-steps (of this fragment group, or the first of the next one)
+                if (grp + 1 < ngrp) load_group(bnxt, f0, grp + 1);
+                else if (next_q < ngroups) load_group(bnxt, ftop - NF * next_q, 0);
+                if (4 * grp + 4 <= kl_last) {
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        double a[MI];
+#pragma unroll
+                        for (int mi = 0; mi < MI; ++mi) a[mi] = sAw[(mi * nks + grp * 4 + kk) * 32];
+#pragma unroll
+                        for (int mi = 0; mi < MI; ++mi)
+#pragma unroll
+                            for (int nf = 0; nf < NF; ++nf) dmma(acc[mi][nf], a[mi], bcur[kk][nf]);
+                    }
+                } else {
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        const int ks = grp * 4 + kk;
+                        double a[MI];
+#pragma unroll
+                        for (int mi = 0; mi < MI; ++mi) a[mi] = sAw[(mi * nks + ks) * 32];
+#pragma unroll
+                        for (int nf = 0; nf < NF; ++nf)
+                            if (ks < klim_of(f0 - nf)) {
+#pragma unroll
+                                for (int mi = 0; mi < MI; ++mi) dmma(acc[mi][nf], a[mi], bcur[kk][nf]);
+                            }
+                    }
+                }
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)
+#pragma unroll
+                    for (int nf = 0; nf < NF; ++nf) bcur[kk][nf] = bnxt[kk][nf];
+            }
+            if (f0 == ftop) {
+                // the top fragment holds row N (= alpha: the mean) and nothing past it counts
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int n = f0 * 8 + 2 * t + e;
+#pragma unroll
+                    for (int mi = 0; mi < MI; ++mi) {
+                        const double x = acc[mi][0][e];
+                        if (n < N) sumsq[mi] = fma(x, x, sumsq[mi]);
+                        else if (n == N) meanv[mi] = x;
+                    }
+                }
+            }
+#pragma unroll
+            for (int nf = 0; nf < NF; ++nf) {
+                if (f0 - nf < 0 || (nf == 0 && f0 == ftop)) continue;
+#pragma unroll
+                for (int mi = 0; mi < MI; ++mi)
+                    sumsq[mi] = fma(acc[mi][nf][0], acc[mi][nf][0], fma(acc[mi][nf][1], acc[mi][nf][1], sumsq[mi]));
+            }
+            ++idx;
+            q = next_q;
+        }
+    }
+#pragma unroll
+    for (int mi = 0; mi < MI; ++mi) {
+        sumsq[mi] += __shfl_xor_sync(0xffffffffu, sumsq[mi], 1);
+        sumsq[mi] += __shfl_xor_sync(0xffffffffu, sumsq[mi], 2);
+        meanv[mi] += __shfl_xor_sync(0xffffffffu, meanv[mi], 1);   // only one lane of the quad holds column N
+        meanv[mi] += __shfl_xor_sync(0xffffffffu, meanv[mi], 2);
+        if (t == 0) {
+            const int row = wm * 8 * MI + mi * 8 + g;
+            sSq[wn * GP_WT + row] = sumsq[mi];
+            sMn[wn * GP_WT + row] = meanv[mi];
+        }
+    }
+}
+
+// var = diag - sum V^2 clipped at 0, std -> squared, mean: thread tid < GP_WT finishes walker w0 + tid
+template <int GP_WT>
+__device__ __forceinline__ void gp_finish_tile(const PcDesc& pc, const double* sSq, const double* sMn, int tid, long long w0, long long W,
+                                               double* __restrict__ m_out, double* __restrict__ v_out, int Ptot, int col) {
+    if (tid < GP_WT) {
+        const long long w = w0 + tid;
+        if (w < W) {
+            double ss = 0.0, mu = 0.0;
+#pragma unroll
+            for (int o = 0; o < GP_K2_OWNERS; o += 2) {
+                ss += sSq[o * GP_WT + tid] + sSq[(o + 1) * GP_WT + tid];
+                mu += sMn[o * GP_WT + tid] + sMn[(o + 1) * GP_WT + tid];
+            }
+            double var = pc.diag - ss;
+            if (var < 0.0) var = 0.0;                       // _gpr.py:485-491
+            const double sd = sqrt(var);                    // _gpr.py:500 returns the std ...
+            const long long o = w * Ptot + col;
+            m_out[o] = mu;
+            v_out[o] = sd * sd;                             // ... and the reference squares it, emulation.py:499
+        }
+    }
+}
+
 // grid: (ceil(W / GP_WT), n_pc_selected).  pcs[blockIdx.y + pc_first] describes the PC.
 // k_out (optional): (W, k_ld_pc, N) row-major slice for this group, PC index = desc.local.
 // m_out / v_out (optional): (W, Ptot) at column blockIdx.y + pc_first.
@@ -193,10 +355,9 @@ __global__ void __launch_bounds__(GP_WT * 8, GP_WT == 32 ? 2 : 1) gp_predict_ker
     double* sX = sA + (size_t)GP_WT * 4 * nks;
     double* sTh = sX + (size_t)d * N;
     double* sSq = sTh + GP_WT * d;
-    double* sMn = sSq + GP_WT * 4;
+    double* sMn = sSq + GP_WT * 8;
 
     constexpr int GP_THREADS = GP_WT * 8;
-    constexpr int WM = GP_WT / 16;          // warps along the walker rows
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long w0 = (long long)blockIdx.x * GP_WT;
 #ifdef GP_TIMING
@@ -222,10 +383,10 @@ __global__ void __launch_bounds__(GP_WT * 8, GP_WT == 32 ? 2 : 1) gp_predict_ker
 
     // ---- K1 -------------------------------------------------------------------------------------------------
     switch (pc.kind) {   // the kernel kind is a template parameter of the loop so that its four chains interleave
-        case 0: gp_k1_loop<DO_GP, 0>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc); break;
-        case 1: gp_k1_loop<DO_GP, 1>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc); break;
-        case 2: gp_k1_loop<DO_GP, 2>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc); break;
-        default: gp_k1_loop<DO_GP, 3>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc); break;
+        case 0: gp_k1_loop<DO_GP, 0>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
+        case 1: gp_k1_loop<DO_GP, 1>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
+        case 2: gp_k1_loop<DO_GP, 2>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
+        default: gp_k1_loop<DO_GP, 3>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
     }
     if (!DO_GP) return;
     GP_T(1);
@@ -233,142 +394,12 @@ __global__ void __launch_bounds__(GP_WT * 8, GP_WT == 32 ? 2 : 1) gp_predict_ker
     GP_T(2);
 
     // ---- K2 -------------------------------------------------------------------------------------------------
-    // warp (wm, wn): walker rows wm*16.., fragment groups {q : snake(q) == wn}.  The B operand is cut into n-fragments
-    // of 8 rows of L^-1 (fragment f = rows 8f .. 8f+7; row N holds alpha).  Fragment f only needs the k-steps
-    // 0 .. min(ceil(N/4), 2f+2) - 1 (L^-1 is lower triangular) and fragments past row N do not exist, so the fragments
-    // are grouped four at a time from the TOP (group 0 = the four longest) and the groups dealt to the four n-owners
-    // in snake order: every owner gets the same number of DMMAs to within a few per cent (C3: 216..222 fragment
-    // k-steps of 870).  B (L2 resident, shared by every CTA of this PC) is streamed global -> registers in groups
-    // of 4 k-steps, one group ahead of the DMMAs that consume it.
-    const int wm = warp % WM;   // rows wm*16 .. wm*16+15
-    const int wn = warp / WM;   // fragment-group owner 0..3
-    const int g = lane >> 2, t = lane & 3;
-    double sumsq[2] = {0.0, 0.0};
-    double meanv[2] = {0.0, 0.0};
-    const double* sAw = sA + (size_t)(2 * wm) * nks * 32 + lane;
-    const double* Bl = pc.LinvF + lane;
-    const int kfull = (N + 3) >> 2;
-    const int ftop = N >> 3;                        // fragment holding row N
-    const int ngroups = (ftop + 4) >> 2;
-
-    auto group_of = [&](int idx) {   // idx-th fragment group owned by this warp
-        const int blk = idx >> 1;
-        return blk * 8 + ((idx & 1) ? 7 - wn : wn);
-    };
-    auto klim_of = [&](int f) { return f < 0 ? 0 : min(kfull, 2 * f + 2); };
-    // loads are never predicated: past a fragment's triangle the packed operand holds zeros (4*grp+3 < nks always),
-    // and the fragments a bottom group lacks are clamped to fragment 0 and never multiplied
-    auto load_group = [&](double (&bb)[4][4], int f0, int grp) {
-#pragma unroll
-        for (int nf = 0; nf < 4; ++nf) {
-            const double* bp = Bl + ((size_t)max(f0 - nf, 0) * nks + 4 * grp) * 32;
-#pragma unroll
-            for (int kk = 0; kk < 4; ++kk) bb[kk][nf] = __ldg(bp + kk * 32);
-        }
-    };
-
-    int idx = 0;
-    int q = group_of(0);
-    if (q < ngroups) {
-        double bcur[4][4], bnxt[4][4];
-        load_group(bcur, ftop - 4 * q, 0);
-        while (q < ngroups) {
-            const int f0 = ftop - 4 * q;
-            const int ngrp = (klim_of(f0) + 3) >> 2;
-            const int kl3 = klim_of(f0 - 3);       // the shortest fragment of the group
-            double acc[2][4][2];
-#pragma unroll
-            for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-                for (int nf = 0; nf < 4; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
-            const int next_q = group_of(idx + 1);
-            for (int grp = 0; grp < ngrp; ++grp) {
-                // prefetch the next group of k-steps (of this fragment group, or the first of the next one)
-                if (grp + 1 < ngrp) load_group(bnxt, f0, grp + 1);
-                else if (next_q < ngroups) load_group(bnxt, ftop - 4 * next_q, 0);
-                if (4 * grp + 4 <= kl3) {
-#pragma unroll
-                    for (int kk = 0; kk < 4; ++kk) {
-                        double a[2];
-#pragma unroll
-                        for (int mi = 0; mi < 2; ++mi) a[mi] = sAw[(mi * nks + grp * 4 + kk) * 32];
-#pragma unroll
-                        for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-                            for (int nf = 0; nf < 4; ++nf) dmma(acc[mi][nf], a[mi], bcur[kk][nf]);
-                    }
-                } else {
-#pragma unroll
-                    for (int kk = 0; kk < 4; ++kk) {
-                        const int ks = grp * 4 + kk;
-                        double a[2];
-#pragma unroll
-                        for (int mi = 0; mi < 2; ++mi) a[mi] = sAw[(mi * nks + ks) * 32];
-#pragma unroll
-                        for (int nf = 0; nf < 4; ++nf)
-                            if (ks < klim_of(f0 - nf)) {
-#pragma unroll
-                                for (int mi = 0; mi < 2; ++mi) dmma(acc[mi][nf], a[mi], bcur[kk][nf]);
-                            }
-                    }
-                }
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk)
-#pragma unroll
-                    for (int nf = 0; nf < 4; ++nf) bcur[kk][nf] = bnxt[kk][nf];
-            }
-            if (f0 == ftop) {
-                // the top fragment holds row N (= alpha: the mean) and nothing past it counts
-#pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const int n = f0 * 8 + 2 * t + e;
-#pragma unroll
-                    for (int mi = 0; mi < 2; ++mi) {
-                        const double x = acc[mi][0][e];
-                        if (n < N) sumsq[mi] = fma(x, x, sumsq[mi]);
-                        else if (n == N) meanv[mi] = x;
-                    }
-                }
-            }
-#pragma unroll
-            for (int nf = 0; nf < 4; ++nf) {
-                if (f0 - nf < 0 || (nf == 0 && f0 == ftop)) continue;
-#pragma unroll
-                for (int mi = 0; mi < 2; ++mi)
-                    sumsq[mi] = fma(acc[mi][nf][0], acc[mi][nf][0], fma(acc[mi][nf][1], acc[mi][nf][1], sumsq[mi]));
-            }
-            ++idx;
-            q = next_q;
-        }
-    }
+    gp_k2_tile<GP_WT>(pc, sA, warp, lane, sSq, sMn);
     GP_T(3);
-#pragma unroll
-    for (int mi = 0; mi < 2; ++mi) {
-        sumsq[mi] += __shfl_xor_sync(0xffffffffu, sumsq[mi], 1);
-        sumsq[mi] += __shfl_xor_sync(0xffffffffu, sumsq[mi], 2);
-        meanv[mi] += __shfl_xor_sync(0xffffffffu, meanv[mi], 1);   // only one lane of the quad holds column N
-        meanv[mi] += __shfl_xor_sync(0xffffffffu, meanv[mi], 2);
-        if (t == 0) {
-            const int row = wm * 16 + mi * 8 + g;
-            sSq[wn * GP_WT + row] = sumsq[mi];
-            sMn[wn * GP_WT + row] = meanv[mi];
-        }
-    }
     __syncthreads();
     GP_T(4);
-    if (tid < GP_WT) {
-        const long long w = w0 + tid;
-        if (w < W) {
-            const double ss = (sSq[tid] + sSq[GP_WT + tid]) + (sSq[2 * GP_WT + tid] + sSq[3 * GP_WT + tid]);
-            const double mu = (sMn[tid] + sMn[GP_WT + tid]) + (sMn[2 * GP_WT + tid] + sMn[3 * GP_WT + tid]);
-            double var = pc.diag - ss;
-            if (var < 0.0) var = 0.0;                       // _gpr.py:485-491
-            const double sd = sqrt(var);                    // _gpr.py:500 returns the std ...
-            const long long o = w * Ptot + pc_first + blockIdx.y;
-            m_out[o] = mu;
-            v_out[o] = sd * sd;                             // ... and the reference squares it, emulation.py:499
-        }
-    }
+    gp_finish_tile<GP_WT>(pc, sSq, sMn, tid, w0, W, m_out, v_out, Ptot, pc_first + blockIdx.y);
 }
+
 
 }  // namespace bi
