@@ -80,6 +80,8 @@ struct bi_handle_s {
     long long ws_stride = 0;
     size_t chol_smem = 0, gp_smem = 0;
     int gp_wt = 32;
+    int k3_persist = -1;      // covariance assembly: -1 = choose per layout, 0 / 1 = developer override (BI_K3_PERSIST)
+    double k3_block_share = 1.0;
     double* dOutScratch = nullptr;   // staging for *_host outputs (mean / cov / k)
     size_t out_scratch_bytes = 0;
     long long launches = 0;
@@ -550,6 +552,13 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         std::vector<int> omin((size_t)nt), omax((size_t)nt), kminD((size_t)nt, 0), imaxD((size_t)nt, nt - 1),
             kminS((size_t)nt), imaxS((size_t)nt);
         for (int i = 0; i < nt; ++i) { omin[i] = obs[(size_t)i * 32]; omax[i] = obs[(size_t)i * 32 + 31]; }
+        {   // share of the merged covariance's lower tiles that hold an observable block (the rest is zero-filled by K3)
+            const int nt3 = (F + 31) / 32;
+            long long hit = 0;
+            for (int i = 0; i < nt3; ++i)
+                for (int j = 0; j <= i; ++j) hit += omax[j] >= omin[i];
+            h->k3_block_share = (double)hit / ((double)nt3 * (nt3 + 1) / 2);
+        }
         for (int i = 0; i < nt; ++i) {
             int k = 0;
             while (omax[k] < omin[i]) ++k;
@@ -609,6 +618,8 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         CKB(cudaFuncSetAttribute(gp_predict_kernel<true, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
         CKB(cudaFuncSetAttribute(gp_predict_kernel<false, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
     }
+    CKB(cudaFuncSetAttribute(cov_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K3P_SMEM_MAX));
+    if (const char* e = std::getenv("BI_K3_PERSIST")) h->k3_persist = std::atoi(e) != 0;   // developer A/B knob
     {
         const size_t cs = (size_t)std::max(h->K0, 4) * 33 * sizeof(double);
         if (cs > 48 * 1024) CKB(cudaFuncSetAttribute(cov_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cs));
@@ -726,8 +737,19 @@ static int predict_any(bi_handle h, int group, const double* theta, int64_t W, d
         CK(cudaGetLastError());
     }
     if (cov_out) {
-        const size_t smem = (size_t)P.K0 * 33 * sizeof(double);     // v + the 32 x K0 operand tile (<= 48 KB for K0 <= 180)
-        cov_assemble_kernel<<<dim3((P.Fo + 31) / 32, (unsigned)W), 256, smem, s>>>(P);
+        // Measured (1491 walkers, B200): one dense 600-bin block 1.36 ms with the (row tile, walker) grid, 1.03 ms persistent;
+        // 20 observables x 10 bins (46 % of the tiles hold a block) 0.32 vs 0.21 ms; 30 x 20 bins (19 %) 1.00 vs 1.12 ms --
+        // the persistent kernel wins wherever contraction matters, the grid kernel where the launch is mostly zero fill.
+        const size_t psmem = k3p_smem_bytes(P.Fo, P.K0);
+        const bool dense_layout = group >= 0 || h->k3_block_share >= 0.3;
+        if ((h->k3_persist < 0 ? dense_layout : h->k3_persist != 0) && psmem <= K3P_SMEM_MAX) {
+            const long long nt3 = (P.Fo + 31) / 32, items = W * (nt3 * (nt3 + 1) / 2);
+            const long long ctas = std::min<long long>(h->sm_count, (items + K3P_THREADS / 32 - 1) / (K3P_THREADS / 32));
+            cov_persist_kernel<<<(unsigned)ctas, K3P_THREADS, psmem, s>>>(P);
+        } else {
+            const size_t smem = (size_t)P.K0 * 33 * sizeof(double);     // v + the 32 x K0 operand tile (<= 48 KB for K0 <= 180)
+            cov_assemble_kernel<<<dim3((P.Fo + 31) / 32, (unsigned)W), 256, smem, s>>>(P);
+        }
         h->launches++;
         CK(cudaGetLastError());
     }
