@@ -50,7 +50,8 @@ struct bi_handle_s {
     double *dTrow = nullptr, *dTt = nullptr, *dTm = nullptr, *dE = nullptr, *dMeanMerged = nullptr, *dUblk = nullptr;
     double *dSig = nullptr, *dYerr = nullptr, *dATiles = nullptr, *dTmP = nullptr;
     int nTc = 0, chol_impl = 2;
-    size_t pipe_smem = 0;
+    size_t pipe_smem = 0, pipe_smem_wide = 0;
+    int pipe_wide = 0;        // 16-consumer instantiation of K4 available (tail of a launch, launches of <= one walker per SM)
     double a_ndiv = -1.0;
     // experimental data sets for batched closure tests (bi_set_data_sets)
     int n_sets = 0;
@@ -222,7 +223,32 @@ int launch_chol(bi_handle h, const double* dTheta, const double* dM, const doubl
             cudaMemsetAsync(dbg, 0, 64 * 8, s);
             PP.dbg = dbg;
 #endif
-            chol_pipe_kernel<<<grid, PIPE_THREADS, h->pipe_smem, s>>>(PP);
+            // Walkers of a last wave that fills at most half of the resident CTA slots (one walker per SM) go to the
+            // 16-consumer instantiation: alone on its SM a CTA of 8 consumers is no faster than next to a second one.
+            // Measured (C3a, 1024 walkers = 3 full waves + 136): 3.62 -> 3.30 ms.  Only where a panel has more strips than
+            // 8 warps take in a round: with tile skipping (structured mode) or F <= 288 it changes nothing or loses 1-2 %.
+            long long w_tail = 0;
+#ifndef PIPE_TIMING
+            if (h->pipe_wide && mode == BI_MODE_DENSE && h->nt >= 10) {
+                const long long rem = W % h->chol_ctas;
+                if (rem > 0 && rem <= h->sm_count) w_tail = rem;
+            }
+#endif
+            const long long w_main = W - w_tail;
+            if (w_main > 0) {
+                PP.c.W = w_main;
+                chol_pipe_kernel<PIPE_CONSUMERS_MAIN><<<(int)std::min<long long>(w_main, h->chol_ctas), pipe_threads(PIPE_CONSUMERS_MAIN),
+                                                        h->pipe_smem, s>>>(PP);
+            }
+            if (w_tail > 0) {
+                PipeParams PT = PP;
+                PT.c.W = w_tail;
+                PT.c.theta += w_main * h->d; PT.c.m += w_main * h->Ptot; PT.c.v += w_main * h->Ptot; PT.c.logp += w_main;
+                if (PT.c.info) PT.c.info += w_main;
+                if (PT.c.set_id) PT.c.set_id += w_main;
+                chol_pipe_kernel<PIPE_CONSUMERS_WIDE><<<(int)w_tail, pipe_threads(PIPE_CONSUMERS_WIDE), h->pipe_smem_wide, s>>>(PT);
+                if (w_main > 0) h->launches++;
+            }
 #ifdef PIPE_TIMING
             {
                 long long hb[64];
@@ -637,8 +663,15 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         h->pipe_smem = pipe_smem_bytes(Fp, h->nTc * 32);
         if (h->chol_impl == 2 && (h->pipe_smem > 227 * 1024 || nt > 120)) h->chol_impl = 1;
         if (h->chol_impl == 2) {
-            CKB(cudaFuncSetAttribute(chol_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pipe_smem));
-            CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_pipe_kernel, PIPE_THREADS, h->pipe_smem));
+            CKB(cudaFuncSetAttribute(chol_pipe_kernel<PIPE_CONSUMERS_MAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pipe_smem));
+            CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_pipe_kernel<PIPE_CONSUMERS_MAIN>, pipe_threads(PIPE_CONSUMERS_MAIN),
+                                                              h->pipe_smem));
+            h->pipe_smem_wide = pipe_smem_bytes(Fp, h->nTc * 32, PIPE_CONSUMERS_WIDE);
+            h->pipe_wide = h->pipe_smem_wide <= 227 * 1024;
+            if (const char* e = std::getenv("BI_PIPE_WIDE")) { if (std::atoi(e) == 0) h->pipe_wide = 0; }   // developer A/B knob
+            if (h->pipe_wide)
+                CKB(cudaFuncSetAttribute(chol_pipe_kernel<PIPE_CONSUMERS_WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)h->pipe_smem_wide));
             if (occ < 1) {
                 h->err = "pipelined Cholesky kernel does not fit on an SM";
                 return bail(BI_E_UNSUPPORTED);

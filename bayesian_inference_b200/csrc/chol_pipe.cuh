@@ -31,23 +31,27 @@ namespace bi {
 #ifndef PIPE_XBYTES
 #define PIPE_XBYTES (SUB_ELEMS * 8)   // experiment knob: bytes actually copied per A piece
 #endif
-constexpr int PIPE_CONSUMERS = 8;
-constexpr int PIPE_THREADS = (PIPE_CONSUMERS + 2) * 32;   // + producer + factor warp
+// Consumer warps per CTA is a template parameter of the kernel: 8 (two CTAs per SM, the throughput configuration) or 16 (one
+// CTA per SM: a panel needs about two thirds of the lock-step rounds, used for the walkers of a last, less than half filled
+// wave and for launches of at most one walker per SM, where latency is what counts).
+constexpr int PIPE_CONSUMERS_MAIN = 8;
+constexpr int PIPE_CONSUMERS_WIDE = 16;
+__host__ __device__ constexpr int pipe_threads(int nc) { return (nc + 2) * 32; }   // + producer + factor warp
 #ifndef PIPE_NSTAGES
 #define PIPE_NSTAGES 4   // measured: 3, 4, 6 and 8 stages all leave the consumers' wait at 25-30 % -- the ring is not latency bound
 #endif
 constexpr int PIPE_STAGES = PIPE_NSTAGES;
 constexpr int STRIP_ELEMS = TILE_ELEMS / 2;                // 16 x 32 doubles = 4 KB
 constexpr int SUB_ELEMS = STRIP_ELEMS / 2;                 // 16 x 16 doubles = 2 KB: one K half of a strip
-constexpr int STAGE_ELEMS = 2 * SUB_ELEMS + PIPE_CONSUMERS * SUB_ELEMS;   // B piece (2 strips) + 8 A pieces = 20 KB
+__host__ __device__ constexpr int pipe_stage_elems(int nc) { return (2 + nc) * SUB_ELEMS; }   // B piece (2 strips) + one A piece per consumer: 20 KB at 8
 
 __host__ __device__ __forceinline__ int of2_index(int r, int c) {
     return ((((r >> 4) * 8 + (c >> 2)) * 2 + ((r >> 3) & 1)) << 5) + ((r & 7) << 2) + (c & 3);
 }
 
-__host__ __device__ inline size_t pipe_smem_bytes(int Fp, int K0p) {
+__host__ __device__ inline size_t pipe_smem_bytes(int Fp, int K0p, int nc = PIPE_CONSUMERS_MAIN) {
     size_t b = 0;
-    b += sizeof(double) * (size_t)PIPE_STAGES * STAGE_ELEMS;
+    b += sizeof(double) * (size_t)PIPE_STAGES * pipe_stage_elems(nc);
     b += sizeof(double) * TILE_ELEMS;          // sLinv
     b += sizeof(double) * 32 * 33;             // sD
     b += sizeof(double) * 32;                  // sRinv
@@ -335,10 +339,15 @@ __device__ __forceinline__ void strip_trsm_blocked(double (&c)[2][4][2], double 
 // per panel of the first version cost 9 % of the kernel (one more lock-step round on every fourth panel).
 // Row F lives in strip hA of the last row tile.  With structured skipping that strip is the only dense one: in panels
 // that do not couple to the last tile it is swept as a single extra unit, and it always starts at the panel's own kmin.
-__global__ void __launch_bounds__(PIPE_THREADS, 2) chol_pipe_kernel(const PipeParams PP) {
+template <int NC>
+__global__ void __launch_bounds__(pipe_threads(NC), NC == PIPE_CONSUMERS_MAIN ? 2 : 1) chol_pipe_kernel(const PipeParams PP) {
+    constexpr int PIPE_CONSUMERS = NC, PIPE_THREADS = pipe_threads(NC), STAGE_ELEMS = pipe_stage_elems(NC);
     const CholParams& P = PP.c;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* sStage = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+    // 128-byte alignment as an offset into the shared array (rounding the generic address through uintptr_t made every
+    // shared access of this kernel a generic LD.E / ST.E instead of LDS / STS)
+    const unsigned smem_base = (unsigned)__cvta_generic_to_shared(smem_raw);
+    double* sStage = reinterpret_cast<double*>(smem_raw + ((128u - (smem_base & 127u)) & 127u));
     double* sLinv = sStage + (size_t)PIPE_STAGES * STAGE_ELEMS;
     double* sD = sLinv + TILE_ELEMS;
     double* sRinv = sD + 32 * 33;
