@@ -319,10 +319,10 @@ def main() -> None:
                          "d2h_bytes_per_step": int(W * 12), "api": "log_posterior.log_posterior_walkers(numpy) -> numpy",
                          "matches_device_path": same},
                     gpu_launches=int(launches),
-                    roofline={"kernel": "chol_pipe_kernel (K4: assembly + Cholesky + solve + log-det)" if args.mode != "woodbury" else "chol_loglik_kernel<explicit> on P x P (Woodbury); flops counted as the dense path for comparability",
+                    roofline={"kernel": "chol_pipe_kernel (K4: assembly + Cholesky + solve + log-det; per step chol_pipe_kernel<8> on the full waves + chol_pipe_kernel<16> on a last wave of at most one walker per SM, timed together)" if args.mode != "woodbury" else "chol_loglik_kernel<explicit> on P x P (Woodbury); flops counted as the dense path for comparability",
                               "bound": "tensor", "achieved": achieved, "peak": FP64_TENSOR_PEAK_TFLOPS, "unit": "TFLOP/s",
                               "frac": (achieved / FP64_TENSOR_PEAK_TFLOPS) if achieved else None, "traffic": traffic,
-                              "traffic_unit": "bytes per launch (dram read+write, ncu capture of the same command)",
+                              "traffic_unit": "bytes per step of K4 (dram read+write of its launches, ncu capture of the same command)",
                               "peak_source": "FP64 DMMA microbenchmark on this pool's B200 (profiles/r01_fp64_peak_microbench.txt); "
                                              "MEASURED_PEAKS.json holds no FP64 figure; cuBLAS DGEMM sustained = "
                                              f"{FP64_DGEMM_TFLOPS} TFLOP/s",
