@@ -283,3 +283,38 @@ def test_kat_cuda_path_closed_form_answers():
             assert np.count_nonzero(cov[i] - np.diag(np.diag(cov[i]))) == 0
             want = -0.5 * np.sum((mean[i] - z["y"]) ** 2 / c) - 0.5 * np.sum(np.log(c))
             assert abs(lp[i] - want) < 1e-11 * abs(want), (mode, lp[i], want)
+
+
+def test_wave_tail_instantiation_equals_main_instantiation(c3a):
+    # K4 runs the walkers of a last, at most half filled wave on its 16-consumer instantiation (one CTA per SM) and the
+    # rest on the 8-consumer one (two CTAs per SM): the same arithmetic in the same order, so a walker's value must not
+    # depend on which of the two evaluated it.  Batch sizes on both sides of every split point (148 SMs, 296 slots).
+    a, _, dev = c3a
+    full = dev.log_posterior(a.theta, n_div=1.0)
+    slots, sms = dev.query(5), dev.query(4)          # resident K4 CTAs, SMs (bi_query)
+    for W in (1, 5, sms, sms + 1, slots - 1, slots, slots + 1, slots + sms, slots + sms + 1, 2 * slots + 7):
+        if W > a.theta.shape[0]:
+            continue
+        assert np.array_equal(dev.log_posterior(a.theta[:W], n_div=1.0), full[:W]), W
+        assert np.array_equal(dev.log_posterior(a.theta[-W:], n_div=1.0), full[-W:]), W
+
+
+@pytest.mark.parametrize("name", ["TOY", "C1", "C3B"])
+def test_covariance_kernels_agree(name, monkeypatch):
+    # predict(): the persistent per-warp kernel (T resident in shared memory) and the (row tile, walker) grid kernel are
+    # two launch shapes of the same per-tile arithmetic -- bit-identical covariance, merged and per group
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    a = synthetic.generate(name, n_walkers=37) if name != "TOY" else synthetic.generate(name)
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max,
+                     experimental_results=a.experimental_results, sigma_exp=a.sigma_exp)
+    inside = np.all((a.theta > a.min) & (a.theta < a.max), axis=1)
+    th = np.ascontiguousarray(a.theta[inside][:37])
+    out = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("BI_K3_PERSIST", flag)
+        with DeviceEmulator(img) as dev:
+            out[flag] = (dev.predict(th, n_div=float(len(th))), dev.predict_group(0, th, n_div=1.0))
+    for k in (0, 1):                    # merged, group 0
+        for j in (0, 1):                # mean, covariance
+            assert np.array_equal(out["0"][k][j], out["1"][k][j]), (k, j)
