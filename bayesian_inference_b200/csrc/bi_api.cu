@@ -25,6 +25,19 @@ using namespace bi;
 
 namespace {
 
+// The dynamic shared-memory limit of a kernel is an attribute of the FUNCTION on the current device, shared by every handle
+// of the process.  Setting it to what the handle being created needs would lower it under an older handle of a larger
+// problem (its next launch then fails with "invalid argument"), so it is always raised to the device's opt-in maximum;
+// what a launch actually asks for is checked against that maximum where the handle is built.
+template <class Kernel>
+cudaError_t allow_max_smem(Kernel* kernel) {
+    int dev = 0, optin = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+    return e;
+}
+
 struct GroupImg {
     int N = 0, P = 0, Fg = 0, R = 0, nks = 0, ntn = 0, K0g = 0, pc_off = 0;
     double* dXsT = nullptr;    // (P, d, N)
@@ -446,7 +459,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
             h->err = "n_design too large for the triangular-inverse setup kernel (max 908)";
             return bail(BI_E_UNSUPPORTED);
         }
-        CKB(cudaFuncSetAttribute(tri_invert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)inv_smem));
+        CKB(allow_max_smem(tri_invert_kernel));
         tri_invert_kernel<<<dim3((N + 31) / 32, Pg), 32, inv_smem, h->stream>>>(dL, dX, N);
         CKB(cudaGetLastError());
         const size_t per_pc = (size_t)I.ntn * 4 * I.nks * 32;
@@ -638,21 +651,21 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         return bail(BI_E_UNSUPPORTED);
     }
     if (h->gp_wt == 64) {
-        CKB(cudaFuncSetAttribute(gp_predict_kernel<true, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
-        CKB(cudaFuncSetAttribute(gp_predict_kernel<false, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
+        CKB(allow_max_smem(gp_predict_kernel<true, 64>));
+        CKB(allow_max_smem(gp_predict_kernel<false, 64>));
     } else {
-        CKB(cudaFuncSetAttribute(gp_predict_kernel<true, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
-        CKB(cudaFuncSetAttribute(gp_predict_kernel<false, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->gp_smem));
+        CKB(allow_max_smem(gp_predict_kernel<true, 32>));
+        CKB(allow_max_smem(gp_predict_kernel<false, 32>));
     }
-    CKB(cudaFuncSetAttribute(cov_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K3P_SMEM_MAX));
+    CKB(allow_max_smem(cov_persist_kernel));
     if (const char* e = std::getenv("BI_K3_PERSIST")) h->k3_persist = std::atoi(e) != 0;   // developer A/B knob
     {
         const size_t cs = (size_t)std::max(h->K0, 4) * 33 * sizeof(double);
-        if (cs > 48 * 1024) CKB(cudaFuncSetAttribute(cov_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cs));
+        if (cs > 48 * 1024) CKB(allow_max_smem(cov_assemble_kernel));
     }
     if (h->has_data) {
         h->chol_smem = chol_smem_bytes(Fp, h->K0);
-        CKB(cudaFuncSetAttribute(chol_loglik_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chol_smem));
+        CKB(allow_max_smem(chol_loglik_kernel<false>));
         int occ = 0;
         CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_loglik_kernel<false>, CHOL_THREADS, h->chol_smem));
         if (occ < 1) {
@@ -663,15 +676,14 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         h->pipe_smem = pipe_smem_bytes(Fp, h->nTc * 32);
         if (h->chol_impl == 2 && (h->pipe_smem > 227 * 1024 || nt > 120)) h->chol_impl = 1;
         if (h->chol_impl == 2) {
-            CKB(cudaFuncSetAttribute(chol_pipe_kernel<PIPE_CONSUMERS_MAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pipe_smem));
+            CKB(allow_max_smem(chol_pipe_kernel<PIPE_CONSUMERS_MAIN>));
             CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_pipe_kernel<PIPE_CONSUMERS_MAIN>, pipe_threads(PIPE_CONSUMERS_MAIN),
                                                               h->pipe_smem));
             h->pipe_smem_wide = pipe_smem_bytes(Fp, h->nTc * 32, PIPE_CONSUMERS_WIDE);
             h->pipe_wide = h->pipe_smem_wide <= 227 * 1024;
             if (const char* e = std::getenv("BI_PIPE_WIDE")) { if (std::atoi(e) == 0) h->pipe_wide = 0; }   // developer A/B knob
             if (h->pipe_wide)
-                CKB(cudaFuncSetAttribute(chol_pipe_kernel<PIPE_CONSUMERS_WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)h->pipe_smem_wide));
+                CKB(allow_max_smem(chol_pipe_kernel<PIPE_CONSUMERS_WIDE>));
             if (occ < 1) {
                 h->err = "pipelined Cholesky kernel does not fit on an SM";
                 return bail(BI_E_UNSUPPORTED);
@@ -850,7 +862,8 @@ int bi_predict_host(bi_handle h, const double* theta, int64_t W, double n_div, d
 static cudaError_t raise_explicit_smem(size_t need) {
     static size_t cur = 0;
     if (need <= cur) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(chol_loglik_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
+    if (need > 227 * 1024) return cudaErrorInvalidValue;
+    cudaError_t e = allow_max_smem(chol_loglik_kernel<true>);
     if (e == cudaSuccess) cur = need;
     return e;
 }
@@ -1215,9 +1228,9 @@ template <int KIND>
 static cudaError_t trainer_attrs(bi_trainer t) {
     cudaError_t e = cudaSuccess;
     if (t->smem_grad > 48 * 1024) {
-        e = cudaFuncSetAttribute(gp_grad_kernel<KIND, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_grad);
+        e = allow_max_smem(gp_grad_kernel<KIND, 8>);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(gp_grad_kernel<KIND, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_grad);
+            e = allow_max_smem(gp_grad_kernel<KIND, 16>);
     }
     return e;
 }
@@ -1259,13 +1272,14 @@ int bi_trainer_create(const double* X, int32_t N, int32_t d, const double* Y, in
     if (const char* s = getenv("BI_TRAIN_OCC")) t->occ = std::max(1, std::min(8, atoi(s)));
     t->smem_factor = lml_factor_smem_bytes(N, t->nwarps);
     t->smem_grad = lml_grad_smem_bytes(N, d);
+    if (e == cudaSuccess && (t->smem_factor > 227 * 1024 || t->smem_grad > 227 * 1024)) e = cudaErrorInvalidValue;   // n_design too large
     t->tiles = lml_tiles_doubles(N);
     t->slot = t->tiles;                                  // M = L^-T has as many tiles as the lower triangle
     t->nslots = t->sms * t->occ;
     // the K / K^-1 tiles of a launch group live in HBM: at most ~4 GB of them at a time
     t->chunk_max = std::max<long long>(t->nslots, (long long)((3ull << 30) / (t->tiles * sizeof(double))));     // x2: K and G tiles
     if (e == cudaSuccess && t->smem_factor > 48 * 1024)
-        e = cudaFuncSetAttribute(gp_factor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_factor);
+        e = allow_max_smem(gp_factor_kernel);
     if (e == cudaSuccess) e = kind == 0 ? trainer_attrs<0>(t) : kind == 1 ? trainer_attrs<1>(t) : kind == 2 ? trainer_attrs<2>(t) : trainer_attrs<3>(t);
     if (e == cudaSuccess) e = cudaMalloc(&t->dScratch, sizeof(double) * t->slot * t->nslots);
     if (e != cudaSuccess) {

@@ -318,3 +318,21 @@ def test_covariance_kernels_agree(name, monkeypatch):
     for k in (0, 1):                    # merged, group 0
         for j in (0, 1):                # mean, covariance
             assert np.array_equal(out["0"][k][j], out["1"][k][j]), (k, j)
+
+
+def test_handles_of_different_sizes_coexist(c3a):
+    # the kernels' dynamic shared-memory limit is a per-function attribute shared by all handles of the process: creating
+    # and using a small problem must not break the launches of a larger one created earlier (and vice versa)
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    a, _, big = c3a
+    before = big.log_posterior(a.theta[:64], n_div=1.0)
+    t = synthetic.generate("TOY")
+    timg = image.pack(t.emulation_config, t.emulation_results, min=t.min, max=t.max, experimental_results=t.experimental_results)
+    with DeviceEmulator(timg) as small:
+        s0 = small.log_posterior(t.theta, n_div=1.0)
+        assert np.array_equal(big.log_posterior(a.theta[:64], n_div=1.0), before)
+        mb, cb = big.predict(a.theta[:3], n_div=1.0)
+        assert np.array_equal(small.log_posterior(t.theta, n_div=1.0), s0, equal_nan=True)
+    assert np.array_equal(big.log_posterior(a.theta[:64], n_div=1.0), before)
+    assert mb.shape == (3, 600) and cb.shape == (3, 600, 600)
