@@ -29,6 +29,16 @@ EXPORTS = [
     "bi_trainer_destroy", "bi_trainer_last_error", "bi_trainer_launches",
 ]
 
+# entry points that return an int status (0 ok, <0 bad argument, >0 CUDA error code); named one by one so that adding
+# an export cannot silently shift a return type
+INT_STATUS_EXPORTS = [
+    "bi_kernel_vectors", "bi_kernel_vectors_host", "bi_predict_pc", "bi_predict_pc_host",
+    "bi_predict_group", "bi_predict_group_host", "bi_predict", "bi_predict_host",
+    "bi_log_posterior", "bi_log_posterior_host", "bi_loglikelihood_host",
+    "bi_stretch_propose", "bi_stretch_accept", "bi_set_data_sets", "bi_log_posterior_sets", "bi_stretch_randoms_philox",
+    "bi_trainer_create", "bi_trainer_lml", "bi_trainer_lml_host", "bi_trainer_factor", "bi_trainer_factor_host",
+]
+
 MODE = {"dense": 0, "structured": 1, "woodbury": 2}
 
 
@@ -146,7 +156,7 @@ def load() -> C.CDLL:
     lib.bi_trainer_launches.argtypes = [h]
     lib.bi_trainer_launches.restype = C.c_int64
     lib.bi_stretch_randoms_philox.argtypes = [h, C.c_uint64, C.c_uint64, i32, i32, C.c_double, dp, dp, dp, dp, dp, C.c_void_p]
-    for name in EXPORTS[8:29]:
+    for name in INT_STATUS_EXPORTS:
         getattr(lib, name).restype = C.c_int
     if lib.bi_abi_version() != 1:
         raise BackendUnavailable(f"ABI version mismatch: library {lib.bi_abi_version()}, package 1")

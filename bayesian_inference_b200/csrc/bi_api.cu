@@ -65,7 +65,13 @@ struct bi_handle_s {
     int nTc = 0, chol_impl = 2;
     size_t pipe_smem = 0, pipe_smem_wide = 0;
     int pipe_wide = 0;        // 16-consumer instantiation of K4 available (tail of a launch, launches of <= one walker per SM)
-    double a_ndiv = -1.0;
+    // A tiles (Sigma_exp + blockdiag(U s s^T) / n_div) per divisor: slot 0 is n_div = 1 (what an MCMC evaluates; built
+    // on its first use and never rebuilt, so a captured CUDA graph that reads it stays valid whatever else the handle is asked
+    // afterwards), slots 1.. rotate among the other divisors (log_posterior(X) with the batch-count divisor, predict-style calls).
+    static constexpr int A_SLOTS = 4;
+    double* dASlot[A_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
+    double a_slot_ndiv[A_SLOTS] = {-1.0, -1.0, -1.0, -1.0};
+    unsigned long long a_slot_stamp[A_SLOTS] = {0, 0, 0, 0}, a_clock = 0;
     // experimental data sets for batched closure tests (bi_set_data_sets)
     int n_sets = 0;
     double *dEsets = nullptr, *dYerrSets = nullptr, *dATilesSets = nullptr;
@@ -158,13 +164,28 @@ int ensure_out_scratch(bi_handle h, size_t bytes) {
     return 0;
 }
 
+// Selects (building it on stream s when needed) the A-tile buffer of this divisor and makes it h->dATiles.  A handle is
+// single-stream: calls that overlap on different streams are not supported (include/bi_b200.h).
 int build_a_tiles(bi_handle h, double n_div, cudaStream_t s) {
-    if (h->a_ndiv == n_div) return 0;
+    int slot = -1;
+    if (n_div == 1.0) slot = 0;
+    else
+        for (int i = 1; i < bi_handle_s::A_SLOTS; ++i)
+            if (h->a_slot_ndiv[i] == n_div) slot = i;
+    if (slot < 0) {                                   // least recently used of the rotating slots
+        slot = 1;
+        for (int i = 2; i < bi_handle_s::A_SLOTS; ++i)
+            if (h->a_slot_stamp[i] < h->a_slot_stamp[slot]) slot = i;
+        h->a_slot_ndiv[slot] = -1.0;
+    }
+    h->a_slot_stamp[slot] = ++h->a_clock;
+    h->dATiles = h->dASlot[slot];
+    if (h->a_slot_ndiv[slot] == n_div) return 0;
     const int ntl = h->nt * (h->nt + 1) / 2;
     build_a_tiles_kernel<<<ntl, 256, 0, s>>>(h->dSig, h->dYerr, h->dUblk, n_div, h->F, h->chol_impl == 2 ? 1 : 0, h->dATiles);
     h->launches++;
     CK(cudaGetLastError());
-    h->a_ndiv = n_div;
+    h->a_slot_ndiv[slot] = n_div;
     return 0;
 }
 
@@ -629,7 +650,8 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         } else {
             TRY(upload(h, &h->dYerr, D->y_err, (size_t)F));
         }
-        TRY(dalloc(h, &h->dATiles, (size_t)nt * (nt + 1) / 2 * TILE_ELEMS));
+        for (int i = 0; i < bi_handle_s::A_SLOTS; ++i) TRY(dalloc(h, &h->dASlot[i], (size_t)nt * (nt + 1) / 2 * TILE_ELEMS));
+        h->dATiles = h->dASlot[0];
         CKB(cudaStreamSynchronize(h->stream));
     }
 
@@ -858,14 +880,12 @@ int bi_predict_host(bi_handle h, const double* theta, int64_t W, double n_div, d
     return predict_host(h, -1, theta, W, n_div, mean_out, cov_out);
 }
 
-// the explicit-matrix Cholesky kernel is shared by _loglikelihood and Woodbury: its opt-in smem limit only ever grows
+// the explicit-matrix Cholesky kernel is shared by _loglikelihood and Woodbury.  The limit is an attribute of the function
+// on the CURRENT device (the caller has done cudaSetDevice): it is set unconditionally -- a process-wide high-water mark
+// would skip it on a second device.
 static cudaError_t raise_explicit_smem(size_t need) {
-    static size_t cur = 0;
-    if (need <= cur) return cudaSuccess;
     if (need > 227 * 1024) return cudaErrorInvalidValue;
-    cudaError_t e = allow_max_smem(chol_loglik_kernel<true>);
-    if (e == cudaSuccess) cur = need;
-    return e;
+    return allow_max_smem(chol_loglik_kernel<true>);
 }
 
 // ---- Woodbury mode ---------------------------------------------------------------------------------------------------

@@ -74,23 +74,47 @@ def _group_results(emulation_config, emulation_group_results) -> dict[str, Any]:
     return out
 
 
+def _same_as_image(passed: Optional[Mapping[str, Any]], emulation_config, results: Mapping[str, Any]) -> bool:
+    """True when a caller-supplied ``emulator_cov_unexplained`` is what the PCA objects imply anyway (the usual case:
+    callers pass the output of ``compute_emulator_cov_unexplained``), so the default image serves it."""
+    if not passed:
+        return True
+    for name, gc in emulation_config.emulation_groups_config.items():
+        if name not in passed:
+            raise KeyError(name)            # the reference indexes the dictionary with every group name (emulation.py:446)
+        own = compute_emulator_group_cov_unexplained(gc, results[name])
+        if not _close(passed[name], own):
+            return False
+    return True
+
+
+def _close(a, b) -> bool:
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return a.shape == b.shape and bool(np.allclose(a, b, rtol=1e-13, atol=1e-14 * max(float(np.max(np.abs(b))) if b.size else 0.0, 1e-300)))
+
+
 def device_emulator(emulation_config, emulation_group_results: Mapping[str, Any], *, min=None, max=None,
-                    experimental_results=None, sigma_exp=None) -> DeviceEmulator:
-    """Build (or fetch from the cache) the device image of a whole analysis."""
+                    experimental_results=None, sigma_exp=None, emulator_cov_unexplained=None) -> DeviceEmulator:
+    """Build (or fetch from the cache) the device image of a whole analysis.  A non-empty ``emulator_cov_unexplained``
+    that differs from what the PCA objects imply gets an image of its own (emulation.py:445-448)."""
     first = next(iter(emulation_group_results.values()))
     d = int(np.asarray(first["emulators"][0].X_train_).shape[1])
     lo = np.full(d, -np.inf) if min is None else np.asarray(min, dtype=np.float64)
     hi = np.full(d, np.inf) if max is None else np.asarray(max, dtype=np.float64)
-    key = ("analysis", id(emulation_config), id(emulation_group_results), _DEVICE, experimental_results is not None)
+    override = None if _same_as_image(emulator_cov_unexplained, emulation_config, emulation_group_results) \
+        else emulator_cov_unexplained
+    key = ("analysis", id(emulation_config), id(emulation_group_results), _DEVICE, experimental_results is not None,
+           None if override is None else id(override))
 
     def build():
         img = _image.pack(emulation_config, emulation_group_results, min=lo, max=hi,
-                          experimental_results=experimental_results, sigma_exp=sigma_exp)
+                          experimental_results=experimental_results, sigma_exp=sigma_exp,
+                          emulator_cov_unexplained=override)
         return DeviceEmulator(img, device=_DEVICE)
 
     if experimental_results is not None:
         return build()   # owned by the caller (log_posterior module), not cached here
-    return _remember(key, emulation_group_results, build)
+    return _remember(key, emulation_group_results if override is None else override, build)
 
 
 def predict(parameters: np.ndarray, emulation_config, merge_predictions_over_groups: bool = True,
@@ -101,12 +125,13 @@ def predict(parameters: np.ndarray, emulation_config, merge_predictions_over_gro
 
     merged:     {'central_value': (n, F), 'cov': (n, F, F)}
     not merged: {group: {'central_value': (n, F_g), 'cov': (n, F_g, F_g)}}
-    ``emulator_cov_unexplained`` is accepted for signature compatibility; the device image always carries the
-    truncated-PC covariance computed from the same PCA objects (the reference recomputes it per call).
+    ``emulator_cov_unexplained``: as in the reference (emulation.py:445-448) a non-empty ``{group: (F_g, F_g)}`` is used
+    instead of the truncated-PC covariance the PCA objects imply; ``None`` / empty -> computed from the PCA objects (once,
+    into the device image; the reference recomputes it per call).
     """
     parameters = np.atleast_2d(np.asarray(parameters, dtype=np.float64))
     results = emulation_group_results if emulation_group_results else _group_results(emulation_config, emulation_group_results)
-    dev = device_emulator(emulation_config, results)
+    dev = device_emulator(emulation_config, results, emulator_cov_unexplained=emulator_cov_unexplained)
     if not merge_predictions_over_groups:
         out = {}
         for gi, name in enumerate(dev.group_names):
@@ -122,16 +147,19 @@ def predict_emulation_group(parameters: np.ndarray, results: dict[str, Any], emu
                             n_div: Optional[float] = None) -> dict[str, np.ndarray]:
     """One emulation group in its own feature order (what plot_emulation.py:312,357 calls on the whole design)."""
     parameters = np.atleast_2d(np.asarray(parameters, dtype=np.float64))
-    key = ("group", id(results), int(emulation_group_config.n_pc), _DEVICE)
+    override = emulator_group_cov_unexplained
+    if override is not None and _close(override, compute_emulator_group_cov_unexplained(emulation_group_config, results)):
+        override = None                    # what the PCA object implies anyway: the default image serves it
+    key = ("group", id(results), int(emulation_group_config.n_pc), _DEVICE, None if override is None else id(override))
 
     def build():
-        g = _image.pack_group("group", results, int(emulation_group_config.n_pc))
+        g = _image.pack_group("group", results, int(emulation_group_config.n_pc), cov_unexplained=override)
         Fg, d = g.n_features, g.X.shape[1]
         img = _image.EmulatorImage(d=d, min=np.full(d, -np.inf), max=np.full(d, np.inf), groups=[g],
                                    blocks=np.array([[0, 0, 0, Fg]], dtype=np.int64), n_features=Fg)
         return DeviceEmulator(img, device=_DEVICE)
 
-    dev = _remember(key, results, build)
+    dev = _remember(key, results if override is None else override, build)
     mean, cov = dev.predict_group(0, parameters, n_div=n_div)
     return {"central_value": mean, "cov": cov}
 

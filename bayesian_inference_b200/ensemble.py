@@ -27,6 +27,30 @@ from typing import Callable, Optional
 import numpy as np
 
 
+def walkers_independent(coords: np.ndarray) -> bool:
+    """emcee 3.1.4's initial-state test (``emcee.ensemble.walkers_independent``, the version the reference pins,
+    pdm.lock:504-505): centre the ensemble, scale every column by its largest magnitude and then to unit norm, and ask for
+    a condition number <= 1e8 of that matrix.  (emcee 3.0.x tested ``cond(cov(coords)) > 1e8`` instead, which rejects
+    ensembles whose parameters merely have very different ranges, e.g. jet_substructure.yaml:127-137.)"""
+    coords = np.asarray(coords, dtype=np.float64)
+    if not np.all(np.isfinite(coords)):
+        return False
+    C = coords - np.mean(coords, axis=0)[None, :]
+    C_colmax = np.amax(np.abs(C), axis=0)
+    if np.any(C_colmax == 0):
+        return False
+    C = C / C_colmax
+    C_colsum = np.sqrt(np.sum(C ** 2, axis=0))
+    C = C / C_colsum
+    return bool(np.linalg.cond(C.astype(float)) <= 1e8)
+
+
+def check_initial_state(coords: np.ndarray) -> None:
+    if not walkers_independent(coords):
+        raise ValueError("Initial state has a large condition number. "
+                         "Make sure that your walkers are linearly independent for the best performance")
+
+
 class StretchEnsemble:
     """Minimal stand-in for ``emcee.EnsembleSampler`` with the default ``StretchMove(a=2)``, vectorised callback."""
 
@@ -42,6 +66,14 @@ class StretchEnsemble:
         self.n_log_prob_calls = 0
         self.n_log_prob_rows = 0
         self.reset()
+
+    # The reference pickles the sampler next to mcmc.h5 (mcmc.py:127-132) and plot code calls ``get_chain`` etc. on the
+    # unpickled object: everything that makes up the stored chain pickles, what ties the object to a process (the callback,
+    # the device handle, communicator and device buffers) is dropped.
+    _NOT_PICKLED = ("log_prob_fn", "dev", "group", "_dist", "_buf", "_send", "_recv")
+
+    def __getstate__(self):
+        return {k: (None if k in self._NOT_PICKLED else v) for k, v in self.__dict__.items()}
 
     # ---- storage (emcee backend subset used by mcmc.run_mcmc, mcmc.py:99-116) ---------------------------------
     def reset(self) -> None:
@@ -108,8 +140,7 @@ class StretchEnsemble:
         coords = np.array(initial_state, dtype=np.float64, copy=True)
         if coords.shape != (self.nwalkers, self.ndim):
             raise ValueError("incompatible input dimensions")
-        if np.linalg.cond(np.cov(coords, rowvar=False).reshape(self.ndim, self.ndim)) > 1e8:
-            raise ValueError("Initial state has a large condition number. Make sure that your walkers are linearly independent.")
+        check_initial_state(coords)
         log_prob = self.compute_log_prob(coords) if log_prob0 is None else np.array(log_prob0, dtype=np.float64, copy=True)
         rng = self._random
         W, nd = self.nwalkers, self.ndim
@@ -231,8 +262,7 @@ class DeviceStretchEnsemble(StretchEnsemble):
         W, nd, ns = self.nwalkers, self.ndim, self.nwalkers // 2
         if x0.shape != (W, nd):
             raise ValueError("incompatible input dimensions")
-        if np.linalg.cond(np.cov(x0, rowvar=False).reshape(nd, nd)) > 1e8:
-            raise ValueError("Initial state has a large condition number. Make sure that your walkers are linearly independent.")
+        check_initial_state(x0)
         device = torch.device("cuda", self.dev.device)
         with torch.cuda.device(device):
             coords = torch.from_numpy(x0).to(device)
@@ -318,8 +348,7 @@ class DevicePhiloxEnsemble(DeviceStretchEnsemble):
         W, nd, ns, B = self.nwalkers, self.ndim, self.nwalkers // 2, self.block
         if x0.shape != (W, nd):
             raise ValueError("incompatible input dimensions")
-        if np.linalg.cond(np.cov(x0, rowvar=False).reshape(nd, nd)) > 1e8:
-            raise ValueError("Initial state has a large condition number. Make sure that your walkers are linearly independent.")
+        check_initial_state(x0)
         device = torch.device("cuda", self.dev.device)
         with torch.cuda.device(device):
             f64 = dict(dtype=torch.float64, device=device)
@@ -430,8 +459,7 @@ class BatchedClosureEnsemble:
         if x0.shape != (C_, W, nd):
             raise ValueError("incompatible input dimensions")
         for c in range(C_):
-            if np.linalg.cond(np.cov(x0[c], rowvar=False).reshape(nd, nd)) > 1e8:
-                raise ValueError("Initial state has a large condition number. Make sure that your walkers are linearly independent.")
+            check_initial_state(x0[c])
         device = torch.device("cuda", self.dev.device)
         with torch.cuda.device(device):
             coords = torch.from_numpy(x0.reshape(C_ * W, nd)).to(device)

@@ -160,8 +160,24 @@ def kernel_constants(kernel, d: int) -> tuple[int, np.ndarray, float, float]:
     return kind, ell, const, noise
 
 
-def pack_group(name: str, result: Mapping[str, Any], n_pc: int) -> GroupImage:
-    """Flatten one emulation group's fitted objects (emulation.py:181-190)."""
+def factor_cov_unexplained(U: np.ndarray, n_features: int) -> tuple[np.ndarray, np.ndarray]:
+    """(S_rest, ev_rest) with ``S_rest.T @ diag(ev_rest) @ S_rest == U``: how a caller-supplied truncated-PC covariance
+    (``emulator_cov_unexplained[group]``, emulation.py:445-448, :487-488) enters the device image, which carries that
+    term in factored form.  Symmetric eigendecomposition; eigenvalues of either sign are kept as they are."""
+    U = np.asarray(U, dtype=np.float64)
+    if U.shape != (n_features, n_features):
+        raise ValueError(f"emulator_cov_unexplained has shape {U.shape}, expected ({n_features}, {n_features})")
+    scale = float(np.max(np.abs(U))) if U.size else 0.0
+    if not np.allclose(U, U.T, rtol=0.0, atol=1e-12 * max(scale, 1e-300)):
+        raise ValueError("emulator_cov_unexplained must be symmetric (it is a covariance)")
+    w, V = np.linalg.eigh(0.5 * (U + U.T))
+    keep = np.abs(w) > 0.0
+    return np.ascontiguousarray(V[:, keep].T), np.ascontiguousarray(w[keep])
+
+
+def pack_group(name: str, result: Mapping[str, Any], n_pc: int, cov_unexplained: np.ndarray | None = None) -> GroupImage:
+    """Flatten one emulation group's fitted objects (emulation.py:181-190).  ``cov_unexplained``: use this (F_g, F_g)
+    matrix as the truncated-PC covariance instead of the one the PCA object implies (emulation.py:487-488)."""
     emulators: Sequence[Any] = result["emulators"]
     if len(emulators) < n_pc:
         raise ValueError(f"group {name}: {len(emulators)} emulators for n_pc={n_pc}")
@@ -186,22 +202,31 @@ def pack_group(name: str, result: Mapping[str, Any], n_pc: int) -> GroupImage:
         L[p] = np.tril(gpr.L_)
     comp = np.asarray(pca.components_, dtype=np.float64)
     ev = np.asarray(pca.explained_variance_, dtype=np.float64)
+    S_rest, ev_rest = np.ascontiguousarray(comp[P:]), np.ascontiguousarray(ev[P:])
+    if cov_unexplained is not None:
+        S_rest, ev_rest = factor_cov_unexplained(cov_unexplained, comp.shape[1])
     return GroupImage(name=name, X=X, kind=kind, ell=ell, const=const, noise=noise, alpha=alpha, L=L,
-                      S=np.ascontiguousarray(comp[:P]), S_rest=np.ascontiguousarray(comp[P:]),
-                      ev_rest=np.ascontiguousarray(ev[P:]),
+                      S=np.ascontiguousarray(comp[:P]), S_rest=S_rest, ev_rest=ev_rest,
                       scale=np.asarray(scaler.scale_, dtype=np.float64), mean=np.asarray(scaler.mean_, dtype=np.float64))
 
 
 def pack(emulation_config, emulation_results: Mapping[str, Mapping[str, Any]], *, min, max,
          experimental_results: Mapping[str, np.ndarray] | None = None,
-         sigma_exp: np.ndarray | None = None) -> EmulatorImage:
+         sigma_exp: np.ndarray | None = None,
+         emulator_cov_unexplained: Mapping[str, np.ndarray] | None = None) -> EmulatorImage:
     """Build the image from what ``mcmc.run_mcmc`` hands to ``initialize_pool_variables`` (mcmc.py:48-78).
 
     ``emulation_config`` may be the reference's ``EmulationConfig`` or anything exposing
-    ``emulation_groups_config[g].n_pc`` and ``sort_observables_in_matrix``.
+    ``emulation_groups_config[g].n_pc`` and ``sort_observables_in_matrix``.  A non-empty ``emulator_cov_unexplained``
+    ({group: (F_g, F_g)}) replaces the truncated-PC covariance of every group, as in the reference (emulation.py:445-448:
+    a non-empty dictionary must hold every group).
     """
     names = list(emulation_config.emulation_groups_config.keys())
-    groups = [pack_group(g, emulation_results[g], int(emulation_config.emulation_groups_config[g].n_pc)) for g in names]
+    ucov = emulator_cov_unexplained if emulator_cov_unexplained else {}
+    if ucov and any(g not in ucov for g in names):
+        raise KeyError(f"emulator_cov_unexplained lacks group(s) {[g for g in names if g not in ucov]}")
+    groups = [pack_group(g, emulation_results[g], int(emulation_config.emulation_groups_config[g].n_pc),
+                         cov_unexplained=ucov.get(g)) for g in names]
     bmap = ObservableBlockMap.from_reference(emulation_config.sort_observables_in_matrix)
     blocks = bmap.block_table(names)
     lo = np.asarray(min, dtype=np.float64).ravel()

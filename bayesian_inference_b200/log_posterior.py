@@ -59,7 +59,8 @@ def initialize_pool_variables(local_min, local_max, local_emulation_config, loca
         _device.close()
     _mode = mode
     _device = emulation.device_emulator(local_emulation_config, local_emulation_results, min=local_min, max=local_max,
-                                        experimental_results=local_experimental_results, sigma_exp=sigma_exp)
+                                        experimental_results=local_experimental_results, sigma_exp=sigma_exp,
+                                        emulator_cov_unexplained=local_emulator_cov_unexplained)
 
 
 def device() -> DeviceEmulator:

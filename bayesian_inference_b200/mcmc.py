@@ -15,7 +15,10 @@ Differences, all forced by what is (not) installed here or by the move to the GP
 * ``seed`` makes the run reproducible (the reference never seeds, mcmc.py:88);
 * configuration / emulator / data loading is the reference's own code (out of scope): pass the loaded
   objects in, or leave them ``None`` to have them loaded through the reference package if it is importable;
-* without silx/h5py the result dictionary is written as ``mcmc.npz`` next to where ``mcmc.h5`` would go.
+* ``mcmc.h5`` is written by the reference's writer (silx) when importable, else by an h5py restatement with the same
+  keys and nesting; with neither library installed the same dictionary goes to ``mcmc.npz``;
+* the sampler object pickled to ``config.sampler_outputfile`` exposes ``get_chain / get_log_prob /
+  acceptance_fraction / flatchain`` like the emcee sampler the reference pickles (mcmc.py:127-132).
 """
 from __future__ import annotations
 
@@ -32,25 +35,74 @@ from .ensemble import BatchedClosureEnsemble, DeviceStretchEnsemble, ShardedLogP
 logger = logging.getLogger(__name__)
 
 
+def write_dict_to_h5(results: dict[str, Any], output_dir: str, filename: str) -> str:
+    """The reference's ``data_IO.write_dict_to_h5`` (data_IO.py:217-236: silx ``dicttoh5(results, path,
+    update_mode='modify')``) restated on h5py: nested dictionaries become groups, arrays and scalars datasets under their
+    key, existing entries of the same name are replaced, ``None`` (``autocorrelation_time`` of a short chain, mcmc.py:118)
+    is not written.  ``silx.io.dictdump.h5todict`` -- what ``plot_mcmc.py`` reads with -- returns the same dictionary."""
+    import h5py
+
+    os.makedirs(output_dir, exist_ok=True)
+    path = os.path.join(output_dir, filename)
+
+    def put(group, d):
+        for k, v in d.items():
+            if v is None:
+                continue
+            if k in group:
+                del group[k]
+            if isinstance(v, dict):
+                put(group.create_group(k), v)
+            else:
+                a = np.asarray(v)
+                group.create_dataset(k, data=a.astype("S") if a.dtype.kind == "U" else a)
+
+    with h5py.File(path, "a") as f:
+        put(f, results)
+    return path
+
+
+def read_dict_from_h5(input_dir: str, filename: str) -> dict[str, Any]:
+    """Inverse of ``write_dict_to_h5`` (the reference's ``data_IO.read_dict_from_h5``, data_IO.py:239-257)."""
+    import h5py
+
+    def get(group):
+        return {k: (get(v) if isinstance(v, h5py.Group) else v[()]) for k, v in group.items()}
+
+    with h5py.File(os.path.join(input_dir, filename), "r") as f:
+        return get(f)
+
+
 def _write_results(output_dict: dict[str, Any], config) -> str:
+    """``mcmc.h5`` with the reference's keys (mcmc.py:111-125) through, in this order: the reference's own writer when the
+    reference package and silx are importable; the h5py restatement above; and only when neither HDF5 library is installed
+    (the case in this image: ``import h5py`` / ``import silx`` fail here and on the GPU box) the same dictionary as
+    ``mcmc.npz``.  Only a missing module selects the next writer -- I/O errors propagate."""
     out_dir = getattr(config, "mcmc_output_dir", None) or getattr(config, "output_dir", ".")
     os.makedirs(out_dir, exist_ok=True)
     try:
         from bayesian_inference import data_IO  # the reference's writer, when its dependencies exist
-
+    except ImportError:
+        data_IO = None
+    if data_IO is not None:
         data_IO.write_dict_to_h5(output_dict, out_dir, "mcmc.h5", verbose=True)
         return os.path.join(out_dir, "mcmc.h5")
-    except Exception:
-        path = os.path.join(out_dir, "mcmc.npz")
-        flat = {}
-        for k, v in output_dict.items():
-            if isinstance(v, dict):
-                for kk, vv in v.items():
-                    flat[f"{k}/{kk}"] = np.asarray(vv)
-            elif v is not None:
-                flat[k] = np.asarray(v)
-        np.savez(path, **flat)
-        return path
+    try:
+        import h5py  # noqa: F401
+    except ImportError:
+        h5py = None
+    if h5py is not None:
+        return write_dict_to_h5(output_dict, out_dir, "mcmc.h5")
+    path = os.path.join(out_dir, "mcmc.npz")
+    flat = {}
+    for k, v in output_dict.items():
+        if isinstance(v, dict):
+            for kk, vv in v.items():
+                flat[f"{k}/{kk}"] = np.asarray(vv)
+        elif v is not None:
+            flat[k] = np.asarray(v)
+    np.savez(path, **flat)
+    return path
 
 
 def run_mcmc(config, closure_index: int = -1, *, emulation_config=None, emulation_results=None,
@@ -135,9 +187,8 @@ def run_mcmc(config, closure_index: int = -1, *, emulation_config=None, emulatio
         sampler_file = getattr(config, "sampler_outputfile", None)
         if sampler_file:
             os.makedirs(os.path.dirname(sampler_file) or ".", exist_ok=True)
-            with open(sampler_file, "wb") as f:
-                pickle.dump({"chain": output_dict["chain"], "log_prob": output_dict["log_prob"],
-                             "acceptance_fraction": output_dict["acceptance_fraction"]}, f)
+            with open(sampler_file, "wb") as f:      # mcmc.py:127-132: the sampler object (get_chain, get_log_prob, ...)
+                pickle.dump(sampler, f)
     output_dict["n_log_prob_rows"] = sampler.n_log_prob_rows
     logger.info("Done.")
     return output_dict
@@ -155,6 +206,11 @@ def run_mcmc_closures(config, pseudodata, *, emulation_config, emulation_results
     ``run_mcmc(config, closure_index=i, seed=seeds[i])`` produces.  Returns one reference-style output dictionary per
     closure test (nothing is written).
     """
+    if sigma_exp is not None:
+        # the data-set path carries one diag(y_err**2) per pseudo-data set (bi_set_data_sets); a shared dense Sigma_exp
+        # would silently be dropped there, and chain i would no longer be run_mcmc(closure_index=i, sigma_exp=...)
+        raise ValueError("run_mcmc_closures: a dense sigma_exp is not supported on the batched data-set path; "
+                         "run the closure tests one by one with run_mcmc(..., sigma_exp=...)")
     par = config.analysis_config["parameterization"][config.parameterization]
     lo, hi = np.asarray(par["min"], dtype=np.float64), np.asarray(par["max"], dtype=np.float64)
     ndim, W, C_ = len(par["names"]), config.n_walkers, len(pseudodata)

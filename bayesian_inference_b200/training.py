@@ -20,6 +20,8 @@ the fitted log-marginal-likelihood is not below scikit-learn's.
 """
 from __future__ import annotations
 
+import logging
+
 import ctypes as C
 from dataclasses import dataclass
 from typing import Any, Callable, Mapping
@@ -28,6 +30,8 @@ import numpy as np
 
 from . import _lib
 from .image import KIND_MATERN12, KIND_MATERN32, KIND_MATERN52, KIND_RBF, GroupImage
+
+logger = logging.getLogger(__name__)
 
 
 @dataclass
@@ -159,7 +163,9 @@ def batched_lbfgsb(fun: Callable[[np.ndarray, np.ndarray], tuple[np.ndarray, np.
 
     ``fun(X (b, n), idx (b,)) -> (f (b,), g (b, n))`` evaluates the problems ``idx`` at the rows of ``X``; every call
     is one batch.  Stopping rules are scipy's L-BFGS-B defaults as scikit-learn uses them (``pgtol`` on the projected
-    gradient, ``ftol = factr * eps`` on the relative decrease).  Returns (x, f, n_iterations, n_batches)."""
+    gradient, ``ftol = factr * eps`` on the relative decrease).  Returns (x, f, n_iterations, n_batches); after the call
+    ``batched_lbfgsb.last_converged`` (B,) tells which problems met a stopping rule (False: still moving at ``maxiter`` --
+    scipy would have carried on up to its 15000 iterations -- or no acceptable step within ``maxls`` trials)."""
     x = np.clip(np.array(x0, float), lo, hi)
     B, n = x.shape
     lo = np.broadcast_to(np.asarray(lo, float), (B, n))
@@ -172,6 +178,7 @@ def batched_lbfgsb(fun: Callable[[np.ndarray, np.ndarray], tuple[np.ndarray, np.
     rho = np.zeros((B, m))
     active = np.isfinite(f)
     nit = np.zeros(B, int)
+    gave_up = np.zeros(B, bool)
     for it in range(maxiter):
         pg = np.where(((x <= lo) & (g > 0)) | ((x >= hi) & (g < 0)), 0.0, g)
         active &= np.max(np.abs(pg), axis=1) > pgtol
@@ -223,7 +230,9 @@ def batched_lbfgsb(fun: Callable[[np.ndarray, np.ndarray], tuple[np.ndarray, np.
         small = (f - fn) <= ftol * np.maximum(np.maximum(np.abs(f), np.abs(fn)), 1.0)
         nit[moved] += 1
         x[moved], f[moved], g[moved] = xn[moved], fn[moved], gn[moved]
+        gave_up |= active & stalled
         active &= ~stalled & ~small
+    batched_lbfgsb.last_converged = ~active & ~gave_up & np.isfinite(f)
     return x, f, nit, nbatch
 
 
@@ -238,6 +247,7 @@ class FittedGPs:
     alpha: np.ndarray        # (P, N)        alpha_
     n_batches: int = 0       # batched objective launches the optimiser needed
     n_evaluations: int = 0   # hyper-parameter vectors evaluated in total
+    n_unconverged: int = 0   # winning starts that had not met a stopping rule when the optimiser stopped (maxiter / line search)
 
     @property
     def ell(self) -> np.ndarray:
@@ -299,11 +309,16 @@ def fit_gps(design, Y_pca_T, spec: KernelSpec, alpha: float, n_restarts: int = 0
     try:
         if Pl > 0:
             xs, fs, _, nbatch = batched_lbfgsb(neg, starts[p0:p1].reshape(Pl * R, -1), lo, hi, maxiter=maxiter)
+            conv = batched_lbfgsb.last_converged.reshape(Pl, R)
             fs = np.where(np.isfinite(fs), fs, np.inf).reshape(Pl, R)
             best = np.argmin(fs, axis=1)
+            n_unconv = int(np.count_nonzero(~conv[np.arange(Pl), best]))
+            if n_unconv:
+                logger.warning(f"fit_gps: the best start of {n_unconv} of {Pl} components had not converged after "
+                               f"{maxiter} iterations (scipy's L-BFGS-B would continue up to 15000); raise maxiter")
             theta = xs.reshape(Pl, R, -1)[np.arange(Pl), best]
         else:
-            theta, fs, best, nbatch = np.empty((0, spec.n_hyper)), np.empty((0, R)), np.empty(0, int), 0
+            theta, fs, best, nbatch, n_unconv = np.empty((0, spec.n_hyper)), np.empty((0, R)), np.empty(0, int), 0, 0
         if trainer is not None and Pl > 0:
             lml, L, al = trainer.factor(theta, np.arange(p0, p1, dtype=np.int32))
         else:                                      # host-logic tests: the caller's objective has no factor output
@@ -314,10 +329,10 @@ def fit_gps(design, Y_pca_T, spec: KernelSpec, alpha: float, n_restarts: int = 0
     if world > 1:
         import torch.distributed as dist
         parts: list[Any] = [None] * world
-        dist.all_gather_object(parts, (theta, lml, L, al, nbatch, nev))
+        dist.all_gather_object(parts, (theta, lml, L, al, nbatch, nev, n_unconv))
         theta, lml, L, al = (np.concatenate([p[i] for p in parts if len(p[0])], axis=0) for i in range(4))
-        nbatch, nev = max(p[4] for p in parts), sum(p[5] for p in parts)
-    return FittedGPs(spec, X, theta, lml, L, al, n_batches=nbatch, n_evaluations=nev)
+        nbatch, nev, n_unconv = max(p[4] for p in parts), sum(p[5] for p in parts), sum(p[6] for p in parts)
+    return FittedGPs(spec, X, theta, lml, L, al, n_batches=nbatch, n_evaluations=nev, n_unconverged=n_unconv)
 
 
 def _dist_rank_world() -> tuple[int, int]:
@@ -330,9 +345,14 @@ def _dist_rank_world() -> tuple[int, int]:
     return 0, 1
 
 
-def pca_transform(Y, n_pc: int, max_n_components: int | None = None):
+def pca_transform(Y, n_pc: int, max_n_components: int | None = None, sign_rule: str = "u"):
     """StandardScaler + PCA(svd_solver='full', whiten=False) as emulation.py:107-122 applies them, by one SVD.
-    Returns (Y_pca_truncated (N, n_pc), components (Q, F), explained_variance (Q,), scale (F,), mean (F,))."""
+    Returns (Y_pca_truncated (N, n_pc), components (Q, F), explained_variance (Q,), scale (F,), mean (F,)).
+
+    ``sign_rule``: how the sign of each component is fixed.  'u' (default) is scikit-learn 1.3.0's -- the version the
+    reference pins (pdm.lock:1998) -- ``svd_flip(U, Vt)`` with ``u_based_decision=True``: the entry of largest magnitude in
+    every column of U is made positive.  'v' is scikit-learn >= 1.5's rule (largest entry of every row of Vt).  The final
+    mean and covariance do not depend on it; per-PC quantities (targets, components) compared against pickles do."""
     Y = np.asarray(Y, float)
     mean = Y.mean(axis=0)
     scale = Y.std(axis=0)
@@ -340,7 +360,12 @@ def pca_transform(Y, n_pc: int, max_n_components: int | None = None):
     Z = (Y - mean) / scale
     Zc = Z - Z.mean(axis=0)
     U, sv, Vt = np.linalg.svd(Zc, full_matrices=False)
-    sign = np.sign(Vt[np.arange(Vt.shape[0]), np.argmax(np.abs(Vt), axis=1)])     # sklearn svd_flip, v-based
+    if sign_rule == "u":
+        sign = np.sign(U[np.argmax(np.abs(U), axis=0), np.arange(U.shape[1])])     # sklearn 1.3.0 svd_flip, u-based
+    elif sign_rule == "v":
+        sign = np.sign(Vt[np.arange(Vt.shape[0]), np.argmax(np.abs(Vt), axis=1)])  # sklearn >= 1.5 svd_flip, v-based
+    else:
+        raise ValueError("sign_rule must be 'u' or 'v'")
     sign[sign == 0] = 1.0
     U, Vt = U * sign, Vt * sign[:, None]
     Q = len(sv) if max_n_components is None else min(len(sv), int(max_n_components))

@@ -22,7 +22,10 @@
  *     (L^-1 per principal component, tiled Sigma_exp / unexplained covariance / inverse-PCA matrices);
  *   - functions without the _host suffix take DEVICE pointers on the handle's device, enqueue on `stream`
  *     (a cudaStream_t passed as void*; NULL is CUDA's default stream, as everywhere in the runtime API) and return
- *     without synchronising; their scratch buffers are per handle, so calls on one handle must be stream-ordered;
+ *     without synchronising; their scratch buffers are per handle, so calls on one handle must be stream-ordered
+ *     (one stream at a time).  The theta-independent tiles Sigma_exp + U / n_div are kept per divisor: the buffer of
+ *     n_div = 1 is built once and never rewritten, so a CUDA graph captured around bi_log_posterior(n_div = 1) stays
+ *     valid when the same handle is later asked for other divisors;
  *   - functions with the _host suffix take HOST pointers, copy in, run, copy out and synchronise before returning;
  *   - return value: 0 = ok, < 0 = BI_E_* (bad argument / state), > 0 = a cudaError_t value.
  *     bi_last_error(h) returns a static description of the last failure on that handle;

@@ -76,3 +76,19 @@ def test_no_cpu_fallback_when_library_missing(monkeypatch, tmp_path):
     monkeypatch.setattr(_lib, "LIB_PATH", tmp_path / "nope.so")
     with pytest.raises(_lib.BackendUnavailable):
         _lib.load()
+
+
+def test_return_types_follow_the_header(lib):
+    """Every entry point the header declares as returning ``int`` is typed ``c_int`` in the loader (an explicit list,
+    not a slice of the export list), ``int64_t`` -> ``c_int64``, ``const char*`` -> ``c_char_p``, ``void`` -> None."""
+    text = re.sub(r"/\*.*?\*/", "", _lib.HEADER.read_text(), flags=re.S)
+    decl = dict((name, ret.strip()) for ret, name in re.findall(r"^((?:const\s+char\s*\*|int64_t|int|void))\s+(bi_[a-z_]+)\s*\(", text, flags=re.M))
+    assert sorted(decl) == sorted(_lib.EXPORTS)
+    want = {"int": C.c_int, "int64_t": C.c_int64, "void": None}
+    for name, ret in decl.items():
+        got = getattr(lib, name).restype
+        if ret.startswith("const"):
+            assert got is C.c_char_p, name
+        else:
+            assert got is want[ret], (name, ret, got)
+    assert set(_lib.INT_STATUS_EXPORTS) <= {n for n, r in decl.items() if r == "int"}

@@ -95,6 +95,62 @@ def test_run_mcmc_driver_sequence(monkeypatch, tmp_path):
     again = mcmc.run_mcmc(cfg, emulation_config=object(), emulation_results={}, experimental_results={}, seed=5, write=False, sampler="host")
     assert np.array_equal(out["chain"], again["chain"])
     assert (tmp_path / "mcmc.npz").exists() or (tmp_path / "mcmc.h5").exists()
+    import pickle
+
+    with open(tmp_path / "s.pkl", "rb") as f:              # mcmc.py:127-132: the pickled object answers like the sampler
+        back = pickle.load(f)
+    assert np.array_equal(back.get_chain(), out["chain"]) and np.array_equal(back.get_log_prob(), out["log_prob"])
+    assert np.array_equal(back.acceptance_fraction, out["acceptance_fraction"])
+    assert back.get_chain(flat=True, discard=1, thin=2).shape == (2 * 8, 3) and back.log_prob_fn is None
+    with pytest.raises(ValueError, match="sigma_exp"):
+        mcmc.run_mcmc_closures(cfg, [{}], emulation_config=object(), emulation_results={}, sigma_exp=np.eye(3))
+
+
+def test_write_results_only_falls_back_on_missing_modules(monkeypatch, tmp_path):
+    """I/O errors of the HDF5 writers propagate: only ImportError selects the next writer."""
+    import builtins
+    import sys
+
+    from bayesian_inference_b200 import mcmc
+
+    cfg = types.SimpleNamespace(mcmc_output_dir=str(tmp_path))
+    fake = types.ModuleType("bayesian_inference")
+    fake.data_IO = types.SimpleNamespace(write_dict_to_h5=lambda *a, **k: (_ for _ in ()).throw(OSError("disk full")))
+    monkeypatch.setitem(sys.modules, "bayesian_inference", fake)
+    monkeypatch.setitem(sys.modules, "bayesian_inference.data_IO", fake.data_IO)
+    with pytest.raises(OSError, match="disk full"):
+        mcmc._write_results({"chain": np.zeros((2, 4, 3))}, cfg)
+    assert not (tmp_path / "mcmc.npz").exists()
+    monkeypatch.delitem(sys.modules, "bayesian_inference")
+    monkeypatch.delitem(sys.modules, "bayesian_inference.data_IO")
+    real_import = builtins.__import__
+
+    def no_hdf5(name, *a, **k):
+        if name.split(".")[0] in ("bayesian_inference", "h5py", "silx"):
+            raise ImportError(name)
+        return real_import(name, *a, **k)
+
+    monkeypatch.setattr(builtins, "__import__", no_hdf5)
+    path = mcmc._write_results({"chain": np.zeros((2, 4, 3)), "autocorrelation_time": None,
+                                "experimental_pseudodata": {"y": np.ones(5), "y_err": np.ones(5)}}, cfg)
+    assert path.endswith("mcmc.npz")
+    with np.load(path) as z:
+        assert sorted(z.files) == ["chain", "experimental_pseudodata/y", "experimental_pseudodata/y_err"]
+
+
+def test_mcmc_h5_layout_round_trip(tmp_path):
+    """mcmc.h5 with the reference's keys (mcmc.py:111-125) written by the h5py restatement of data_IO.write_dict_to_h5."""
+    pytest.importorskip("h5py")
+    from bayesian_inference_b200 import mcmc
+
+    d = {"chain": np.random.RandomState(0).rand(5, 8, 3), "acceptance_fraction": np.linspace(0, 1, 8),
+         "log_prob": np.random.RandomState(1).rand(5, 8), "autocorrelation_time": None, "design_point": np.arange(3.0),
+         "experimental_pseudodata": {"y": np.ones(4), "y_err": np.full(4, 0.1)}}
+    mcmc.write_dict_to_h5(d, str(tmp_path), "mcmc.h5")
+    mcmc.write_dict_to_h5({"chain": d["chain"] * 2}, str(tmp_path), "mcmc.h5")          # update_mode='modify': replaced
+    back = mcmc.read_dict_from_h5(str(tmp_path), "mcmc.h5")
+    assert sorted(back) == ["acceptance_fraction", "chain", "design_point", "experimental_pseudodata", "log_prob"]
+    assert np.array_equal(back["chain"], d["chain"] * 2) and np.array_equal(back["experimental_pseudodata"]["y_err"], d["experimental_pseudodata"]["y_err"])
 
 
 # ---- world_size-2 gloo: sharded log-probability and replicated sampler ------------------------------------------------
@@ -193,3 +249,33 @@ def test_philox_restatement_known_answer_vectors():
     assert np.all(r["c_idx"][:, 0] % 2 == 1) and np.all(r["c_idx"][:, 1] % 2 == 0)      # partners from the other half
     later = ph.stretch_randoms(seed=5, step0=5, nsteps=2, nwalkers=12, ndim=3)          # a step does not depend on the block
     assert all(np.array_equal(later[k], r[k][2:]) for k in r)
+
+
+def test_initial_state_check_is_emcee_3_1_4():
+    """The reference pins emcee 3.1.4 (pdm.lock:504-505): ``walkers_independent`` normalises every column before it asks
+    for the condition number, so parameters of very different ranges (jet_substructure.yaml:127-137: 0.4 ... 100) and the
+    tight cluster of the burn-in re-seed (mcmc.py:99) are accepted, while a truly degenerate ensemble is refused."""
+    from bayesian_inference_b200.ensemble import check_initial_state, walkers_independent
+
+    rng = np.random.RandomState(3)
+    scales = np.array([1e-5, 0.4, 100.0, 1e6])
+    wide = rng.uniform(0, 1, (40, 4)) * scales                     # raw covariance condition number ~1e22
+    assert np.linalg.cond(np.cov(wide, rowvar=False)) > 1e8        # what emcee 3.0.x (and round 1 here) tested
+    assert walkers_independent(wide)
+    base = rng.uniform(0, 1, 4) * scales                           # a strongly correlated, tight cluster around one point
+    z = rng.normal(size=(40, 1))
+    cluster = base + (z + 1e-3 * rng.normal(size=(40, 4))) * 1e-6 * scales
+    assert np.linalg.cond(np.cov(cluster, rowvar=False)) > 1e8
+    assert walkers_independent(cluster)
+    check_initial_state(cluster)
+    s = StretchEnsemble(40, 4, lambda x: -0.5 * np.sum((x / scales) ** 2, axis=1), seed=1)
+    s.run_mcmc(wide, 3)                                            # round 1's check raised here
+    degenerate = np.repeat(rng.uniform(0, 1, (1, 4)), 40, axis=0)
+    assert not walkers_independent(degenerate)                     # a column without spread
+    collinear = rng.uniform(0, 1, (40, 1)) * np.ones((1, 4))
+    assert not walkers_independent(collinear)                      # exactly dependent columns
+    bad = wide.copy()
+    bad[3, 1] = np.inf
+    assert not walkers_independent(bad)
+    with pytest.raises(ValueError, match="condition number"):
+        check_initial_state(collinear)

@@ -128,3 +128,45 @@ def test_batched_closure_tests_equal_separate_runs(toy, tmp_path):
         assert np.array_equal(got[sid == c], want, equal_nan=True)
     lp.close()
     emulation.clear_cache()
+
+
+def test_emulator_cov_unexplained_is_honoured(toy):
+    """emulation.py:445-448 / :487-488: a non-empty dictionary replaces the truncated-PC covariance.  Expected values from
+    the oracle on an image packed with the same dictionary (pinned to the reference in tests/test_host_logic.py) and,
+    independently, from the default prediction corrected by (U' - U) s s^T / n_div in numpy."""
+    from bayesian_inference_b200 import emulation, image, log_posterior as lp
+    from oracle import closed_form as cf
+
+    cfgs = toy.emulation_config.emulation_groups_config
+    own = emulation.compute_emulator_cov_unexplained(toy.emulation_config, toy.emulation_results)
+    other = {g: 2.5 * u + 0.02 * np.diag(np.arange(1, u.shape[0] + 1.0)) for g, u in own.items()}
+    th = toy.theta[:10]
+    same = emulation.predict(th, toy.emulation_config, emulation_group_results=toy.emulation_results, emulator_cov_unexplained=own)
+    base = emulation.predict(th, toy.emulation_config, emulation_group_results=toy.emulation_results)
+    assert np.array_equal(same["cov"], base["cov"])                  # the PCA's own matrix: the default image serves it
+    got = emulation.predict(th, toy.emulation_config, emulation_group_results=toy.emulation_results, emulator_cov_unexplained=other)
+    img = image.pack(toy.emulation_config, toy.emulation_results, min=toy.min, max=toy.max, emulator_cov_unexplained=other)
+    mean, cov = cf.predict(img.to_flat(), th)
+    assert fro_err(got["central_value"], mean) < 1e-12 and fro_err(got["cov"], cov) < 1e-12
+    per = emulation.predict(th, toy.emulation_config, merge_predictions_over_groups=False,
+                            emulation_group_results=toy.emulation_results, emulator_cov_unexplained=other)
+    per0 = emulation.predict(th, toy.emulation_config, merge_predictions_over_groups=False,
+                             emulation_group_results=toy.emulation_results)
+    for g in per:
+        s = toy.emulation_results[g]["PCA"]["scaler"].scale_
+        want = per0[g]["cov"] + ((other[g] - own[g]) * np.outer(s, s) / th.shape[0])[None]
+        assert fro_err(per[g]["cov"], want) < 1e-12
+        one = emulation.predict_emulation_group(th, toy.emulation_results[g], cfgs[g], emulator_group_cov_unexplained=other[g])
+        assert fro_err(one["cov"], want) < 1e-12
+    # the same dictionary through initialize_pool_variables (log_posterior.py:80-82)
+    lp.initialize_pool_variables(toy.min, toy.max, toy.emulation_config, toy.emulation_results, toy.experimental_results, other)
+    z = image.pack(toy.emulation_config, toy.emulation_results, min=toy.min, max=toy.max,
+                   experimental_results=toy.experimental_results, emulator_cov_unexplained=other).to_flat()
+    want_lp = cf.log_posterior(z, th)
+    got_lp = lp.log_posterior(th)
+    fin = np.isfinite(want_lp)
+    assert np.array_equal(np.isneginf(got_lp), ~fin) and rel_err(got_lp[fin], want_lp[fin]) < 1e-9
+    lp.initialize_pool_variables(toy.min, toy.max, toy.emulation_config, toy.emulation_results, toy.experimental_results, None)
+    assert rel_err(lp.log_posterior(th)[fin], want_lp[fin]) > 1e-6   # and it changes the answer
+    lp.close()
+    emulation.clear_cache()

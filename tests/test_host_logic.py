@@ -97,3 +97,47 @@ def test_validate_rejects_overlapping_blocks():
 def test_baseline_config_shapes(name, F, P):
     s = synthetic.config(name)
     assert s.n_features == F and s.n_pc_total == P
+
+
+def test_cov_unexplained_override_is_factored_exactly():
+    """A caller-supplied emulator_cov_unexplained (emulation.py:445-448, :487-488) enters the image as an eigen-factor pair
+    that multiplies back to the matrix; asymmetric input and wrong shapes are refused."""
+    rng = np.random.RandomState(0)
+    A = rng.normal(size=(15, 6))
+    U = A @ A.T * 1e-3                     # rank 6, PSD
+    S_rest, ev = image.factor_cov_unexplained(U, 15)
+    assert np.allclose(S_rest.T @ (ev[:, None] * S_rest), U, rtol=0, atol=1e-15 * np.abs(U).max() * 15)
+    with pytest.raises(ValueError):
+        image.factor_cov_unexplained(U[:14, :14], 15)
+    with pytest.raises(ValueError):
+        image.factor_cov_unexplained(U + np.triu(np.ones((15, 15)), 1), 15)
+    a = synthetic.generate("TOY")
+    own = {g: image.pack_group(g, a.emulation_results[g], a.emulation_config.emulation_groups_config[g].n_pc).cov_unexplained()
+           for g in a.emulation_results}
+    other = {g: 3.0 * u + 0.01 * np.eye(u.shape[0]) for g, u in own.items()}
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max, emulator_cov_unexplained=other)
+    for g, gi in zip(img.groups, other):
+        assert np.allclose(g.cov_unexplained(), other[gi], rtol=0, atol=1e-14 * np.abs(other[gi]).max())
+    with pytest.raises(KeyError):
+        image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max, emulator_cov_unexplained={"alpha": other["alpha"]})
+
+
+@pytest.mark.skipif(not rh.available(), reason="reference checkout not present")
+def test_cov_unexplained_override_equals_reference_with_the_same_dictionary():
+    """The reference executed with a non-empty emulator_cov_unexplained == the oracle on the image packed with it."""
+    from oracle import closed_form as cf
+
+    a = synthetic.generate("TOY")
+    ref_em, _, _ = rh.import_reference()
+    cfg = rh.ReferenceConfig(a, "toy_ucov")
+    own = {g: ref_em.compute_emulator_group_cov_unexplained(cfg.emulation_groups_config[g], a.emulation_results[g])
+           for g in a.emulation_results}
+    other = {g: 2.5 * u + 0.02 * np.diag(np.arange(1, u.shape[0] + 1.0)) for g, u in own.items()}
+    th = a.theta[:6]
+    want = ref_em.predict(th, cfg, emulation_group_results=a.emulation_results, emulator_cov_unexplained=other)
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max, emulator_cov_unexplained=other)
+    mean, cov = cf.predict(img.to_flat(), th)
+    assert np.allclose(mean, want["central_value"], rtol=1e-13, atol=0)
+    assert np.linalg.norm(cov - want["cov"]) < 1e-13 * np.linalg.norm(want["cov"])
+    base = ref_em.predict(th, cfg, emulation_group_results=a.emulation_results)
+    assert np.linalg.norm(base["cov"] - want["cov"]) > 1e-3 * np.linalg.norm(want["cov"])      # the override matters

@@ -110,6 +110,28 @@ def test_pca_transform_matches_sklearn():
     sgn = np.sign(np.sum(comps * pca.components_, axis=1))        # a principal axis is defined up to its sign
     assert np.allclose(comps * sgn[:, None], pca.components_, atol=1e-10)
     assert np.allclose(got * sgn[:6], want[:, :6], atol=1e-10)
+    # sign rules: 'u' = scikit-learn 1.3.0 (the reference's pin): largest |entry| of each U column positive;
+    # 'v' = scikit-learn >= 1.5: largest |entry| of each components_ row positive
+    gu = tr.pca_transform(Y, 25, sign_rule="u")[0]
+    assert np.all(gu[np.argmax(np.abs(gu), axis=0), np.arange(gu.shape[1])] > 0)
+    cv = tr.pca_transform(Y, 6, sign_rule="v")[1]
+    assert np.all(cv[np.arange(cv.shape[0]), np.argmax(np.abs(cv), axis=1)] > 0)
+    import sklearn
+    if tuple(int(v) for v in sklearn.__version__.split(".")[:2]) >= (1, 5):
+        assert np.allclose(cv, pca.components_, atol=1e-10)          # same sign, no flip needed
+    with pytest.raises(ValueError):
+        tr.pca_transform(Y, 6, sign_rule="x")
+
+
+def test_batched_lbfgsb_reports_unconverged_problems():
+    """a start still moving at maxiter is flagged instead of passing silently."""
+    A = np.diag([1.0, 1e4])
+    fun = lambda X, idx: (0.5 * np.einsum("bi,ij,bj->b", X, A, X), X @ A)     # noqa: E731
+    x0 = np.array([[5.0, 5.0], [0.0, 0.0]])
+    tr.batched_lbfgsb(fun, x0, -10 * np.ones(2), 10 * np.ones(2), maxiter=1)
+    assert list(tr.batched_lbfgsb.last_converged) == [False, True]           # problem 1 starts at its optimum
+    tr.batched_lbfgsb(fun, x0, -10 * np.ones(2), 10 * np.ones(2), maxiter=200)
+    assert list(tr.batched_lbfgsb.last_converged) == [True, True]
 
 
 # ---- world_size-2 gloo: the components of a fit are sharded over the ranks and gathered ---------------------------------
