@@ -91,6 +91,7 @@ struct bi_handle_s {
     int *dInfoW = nullptr, *dWbK = nullptr;
     int *dObs = nullptr, *dTileOmin = nullptr, *dTileOmax = nullptr;
     int *dKminDense = nullptr, *dImaxDense = nullptr, *dKminStruct = nullptr, *dImaxStruct = nullptr;
+    std::vector<int> hOmin, hOmax, hKmin[2], hImax[2];   // host copies of the tile tables ([0] dense, [1] structured)
     long long max_batch = 4096;
     double *dTheta = nullptr, *dM = nullptr, *dV = nullptr, *dLogp = nullptr;
     int* dInfo = nullptr;
@@ -333,8 +334,36 @@ int bi_abi_version(void) { return BI_ABI_VERSION; }
 
 const char* bi_last_error(bi_handle h) { return h ? h->err.c_str() : "null handle"; }
 
+// DMMA (mma.sync m8n8k4 f64 = 512 flop) instructions chol_pipe_kernel issues for ONE walker inside the prior box, from the
+// same tile tables the kernel walks (kmin / imax / tile_omin / tile_omax): what bench.py reports as `flops_executed`.
+static int64_t k4_dmma_per_walker(bi_handle h, int mode) {
+    if (!h->has_data || h->chol_impl != 2 || mode < 0 || mode > 1 || (int)h->hOmin.size() != h->nt) return -1;
+    const int nt = h->nt, nTc = h->nTc;
+    const std::vector<int>&kmin = h->hKmin[mode], &imax = h->hImax[mode], &omin = h->hOmin, &omax = h->hOmax;
+    const int ra = h->F - (nt - 1) * 32, hA = ra >> 4;
+    int64_t n = 0;
+    for (int j = 0; j < nt; ++j) {
+        const int i_hi = imax[j];
+        const int nreg = 2 * (i_hi - j + 1);
+        const int nunits = nreg + (i_hi < nt - 1 ? 1 : 0);
+        const int qA = (i_hi < nt - 1) ? nreg : 2 * (nt - 1 - j) + hA;
+        const int kA = (j == nt - 1) ? 0 : kmin[j];
+        for (int q = 0; q < nunits; ++q) {
+            const bool aug = q >= nreg;
+            const int i = aug ? nt - 1 : j + (q >> 1);
+            if (!aug && omax[j] >= omin[i]) n += 2ll * nTc * 32;           // theta-dependent T D T^T chunks of this strip
+            const int klo = (q == qA) ? kA : kmin[i];
+            if (j > klo) n += (int64_t)(j - klo) * 64;                       // L_ik L_jk^T chunks
+            if (i != j) n += 40;                                             // blocked triangular solve of the strip
+        }
+        n += 20;                                                             // trailing updates inside the diagonal tile's potrf
+    }
+    return n;
+}
+
 int64_t bi_query(bi_handle h, int what) {
     if (!h) return -1;
+    if (what == 16 || what == 17) return k4_dmma_per_walker(h, what - 16);
     switch (what) {
         case 0: return h->F;
         case 1: return h->Ptot;
@@ -629,6 +658,8 @@ int bi_create(const bi_desc* D, bi_handle* out) {
             while (i + 1 < nt && kminS[i + 1] <= j) ++i;
             imaxS[j] = i;
         }
+        h->hOmin = omin; h->hOmax = omax;
+        h->hKmin[0] = kminD; h->hImax[0] = imaxD; h->hKmin[1] = kminS; h->hImax[1] = imaxS;
         TRY(upload(h, &h->dObs, obs.data(), obs.size()));
         TRY(upload(h, &h->dTileOmin, omin.data(), omin.size()));
         TRY(upload(h, &h->dTileOmax, omax.data(), omax.size()));

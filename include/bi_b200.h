@@ -108,7 +108,9 @@ int  bi_create(const bi_desc* desc, bi_handle* out);
 void bi_destroy(bi_handle h);
 const char* bi_last_error(bi_handle h);
 /* query: what = 0 F, 1 total n_pc, 2 d, 3 n_groups, 4 SM count, 5 Cholesky CTAs resident, 6 scratch bytes,
- *        7 kernels launched since create (launch counter used by bench.py's gpu_launches)                  */
+ *        7 kernels launched since create (launch counter used by bench.py's gpu_launches),
+ *        16 / 17 FP64 tensor instructions (DMMA m8n8k4 = 512 flop each) the fused Cholesky kernel issues per walker in
+ *        BI_MODE_DENSE / BI_MODE_STRUCTURED, counted from the tile tables the kernel walks (bench.py's flops_executed) */
 int64_t bi_query(bi_handle h, int what);
 /* synchronise the handle's own stream */
 int  bi_sync(bi_handle h);

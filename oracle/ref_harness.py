@@ -16,11 +16,22 @@ from typing import Any
 import numpy as np
 
 REFERENCE_SRC = os.environ.get("BI_REFERENCE_SRC", "/root/reference/src")
+BASELINE_REF = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref")
 _H5_STORE: dict[str, Any] = {}
 
 
 def available() -> bool:
     return os.path.isdir(os.path.join(REFERENCE_SRC, "bayesian_inference"))
+
+
+def use_baseline_ref() -> bool:
+    """Point the harness at ``baseline/_ref`` (the copy oracle/make_ref.py makes; it travels to the GPU box, where
+    /root/reference does not exist).  bench.py's CPU arm calls this and never reads /root/reference."""
+    global REFERENCE_SRC
+    if not os.path.isfile(os.path.join(BASELINE_REF, "bayesian_inference", "log_posterior.py")):
+        return False
+    REFERENCE_SRC = BASELINE_REF
+    return True
 
 
 def _install_silx_stub() -> None:

@@ -38,6 +38,44 @@ def test_chain_trace_identical_for_1000_steps(mode):
     assert 0.05 < gpu.acceptance_fraction.mean() < 0.95
 
 
+def test_chain_trace_at_the_c1_shape_vs_oracle():
+    """BASELINE configs[0] (jet_substructure.yaml-shaped: d=4, n_design=230, n_pc=30, n_obs=200; 100 walkers, seed 42;
+    reference driver mcmc.py:83-107): 200 steps of the same StretchEnsemble driven by the CUDA log-posterior (host-side and
+    device-resident sampler) and by the oracle evaluated row by row on a pool of host processes.  The 1,000-step run of the
+    same comparison is tools/chain_trace.py -> profiles/r02_chain_trace_c1.json."""
+    from bayesian_inference_b200 import synthetic
+    from bayesian_inference_b200.device import DeviceEmulator
+    from bayesian_inference_b200.ensemble import DeviceStretchEnsemble
+    from oracle.pool import OraclePool
+
+    a = synthetic.generate("C1")
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max,
+                     experimental_results=a.experimental_results)
+    z = img.to_flat()
+    W, d, nsteps, seed = 100, 4, 200, 42
+    assert (img.n_features, img.groups[0].n_design, img.groups[0].n_pc, img.d) == (200, 230, 30, 4)
+    x0 = np.random.RandomState(seed).uniform(a.min, a.max, (W, d))           # mcmc.py:88
+    with OraclePool(z) as pool:
+        cpu = StretchEnsemble(W, d, pool.log_posterior, seed=seed)
+        cpu.run_mcmc(x0, nsteps)
+    with DeviceEmulator(img) as dev:
+        host = StretchEnsemble(W, d, lambda X: dev.log_posterior(X, n_div=1.0, mode="dense"), seed=seed)
+        host.run_mcmc(x0, nsteps)
+        devs = DeviceStretchEnsemble(W, d, dev, mode="dense", seed=seed)
+        devs.run_mcmc(x0, nsteps)
+    for s in (host, devs):
+        same = np.all(s.get_chain() == cpu.get_chain(), axis=(1, 2))
+        if not same.all():
+            step = int(np.argmin(same))
+            pytest.fail(f"chains diverge at step {step}: max |dlogp| there "
+                        f"{np.nanmax(np.abs(s.get_log_prob()[step] - cpu.get_log_prob()[step])):.3e}")
+        assert np.array_equal(s.acceptance_fraction, cpu.acceptance_fraction)
+        fin = np.isfinite(cpu.get_log_prob())
+        assert np.array_equal(np.isfinite(s.get_log_prob()), fin)
+        assert np.max(np.abs(s.get_log_prob()[fin] - cpu.get_log_prob()[fin]) / np.abs(cpu.get_log_prob()[fin])) < 1e-9
+    assert 0.05 < cpu.acceptance_fraction.mean() < 0.95
+
+
 @pytest.mark.parametrize("mode", ["dense", "woodbury"])
 def test_device_resident_sampler_matches_host_sampler(mode):
     """DeviceStretchEnsemble (propose / accept kernels, state in HBM) == StretchEnsemble driven by the same CUDA

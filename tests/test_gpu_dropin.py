@@ -121,6 +121,21 @@ def test_batched_closure_tests_equal_separate_runs(toy, tmp_path):
             assert np.array_equal(batched[i]["chain"], single["chain"]), (mode, i)
             assert np.array_equal(batched[i]["log_prob"], single["log_prob"])
             assert np.array_equal(batched[i]["acceptance_fraction"], single["acceptance_fraction"])
+        # ... and against the ORACLE: every row of the data-set call is the reference's log_posterior of that walker against
+        # that pseudo-data set (data_IO.py:362-372 -> log_posterior.py:42-101), n_div = 1; likewise the log-probabilities the
+        # batched chains carry at their last step
+        from bayesian_inference_b200 import image
+        from oracle import closed_form as cf
+
+        for c, p in enumerate(pseudo):
+            z_c = image.pack(toy.emulation_config, toy.emulation_results, min=toy.min, max=toy.max,
+                             experimental_results=p).to_flat()
+            want = cf.log_posterior(z_c, th[sid == c], n_div=1.0)
+            fin = np.isfinite(want)
+            assert np.array_equal(np.isneginf(got[sid == c]), ~fin), (mode, c)
+            assert rel_err(got[sid == c][fin], want[fin]) < 1e-9, (mode, c)
+            last_x, last_lp = batched[c]["chain"][-1], batched[c]["log_prob"][-1]
+            assert rel_err(last_lp, cf.log_posterior(z_c, last_x, n_div=1.0)) < 1e-9, (mode, c)
     # the data-set entry point itself against one handle per data set
     for c, p in enumerate(pseudo):
         lp.initialize_pool_variables(toy.min, toy.max, toy.emulation_config, toy.emulation_results, p, None)
