@@ -3,6 +3,8 @@
 known-answer cases.  CPU only."""
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import pytest
 from conftest import fro_err, load_golden, rel_err
@@ -172,3 +174,31 @@ def test_oracle_against_live_reference():
     # and the committed fixture is what the generator produces today
     zg, ref = load_golden("toy")
     assert np.array_equal(zg["g0_L"], z["g0_L"]) and np.allclose(ref["ref_logp_rows"][fin[:24]], want[:24][fin[:24]], rtol=1e-12)
+
+
+def test_reference_pool_runs_the_reference_itself_from_baseline_ref():
+    """bench.py's CPU arm: the reference's unmodified modules in baseline/_ref (oracle/make_ref.py), spawn pool initialised
+    with the reference's initialize_pool_variables, one theta per task -> the golden per-row values."""
+    from bayesian_inference_b200 import synthetic
+    from oracle import make_ref, ref_harness as rh
+    from oracle.ref_pool import ReferencePool
+
+    if not make_ref.make():
+        pytest.skip("no reference checkout and no baseline/_ref")
+    old = rh.REFERENCE_SRC
+    try:
+        assert rh.use_baseline_ref()
+        a = synthetic.generate("TOY", oob_fraction=0.1)
+        _, ref = load_golden("toy")
+        with ReferencePool(a, 2) as pool:
+            got = pool.map_rows(a.theta[:10])
+            one = pool.one_chunk(a.theta[:3])
+        want = ref["ref_logp_rows"][:10]
+        assert np.array_equal(np.isneginf(got), np.isneginf(want))
+        fin = np.isfinite(want)
+        assert np.max(np.abs(got[fin] - want[fin]) / np.abs(want[fin])) < 1e-12
+        assert np.array_equal(one, got[:3], equal_nan=True)
+    finally:
+        rh.REFERENCE_SRC = old
+    sums = open(os.path.join(rh.BASELINE_REF, "bayesian_inference", "SHA256SUMS")).read().split()
+    assert "log_posterior.py" in sums and "emulation.py" in sums
