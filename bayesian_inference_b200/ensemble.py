@@ -222,15 +222,23 @@ class DeviceStretchEnsemble(StretchEnsemble):
     block at a time.  Same RandomState consumption and the same rounded arithmetic as ``StretchEnsemble``, hence the
     same chain (tests/test_gpu_chain.py).  A NaN log-probability raises ``ValueError`` like emcee, at the end of the
     block it occurred in.
+
+    ``graph=True``: state, scratch and the per-block random-number buffers are fixed allocations, so a block of ``block``
+    steps is a fixed launch sequence (the NCCL all-gather included when sharded) and is captured once and replayed as ONE
+    CUDA graph; the host then only uploads the next block's random numbers and replays (the
+    collective is the only thing between the kernels).  A shorter last block runs eagerly.
     """
 
     def __init__(self, nwalkers: int, ndim: int, device_emulator, mode: str = "dense", a: float = 2.0,
                  seed: Optional[int] = None, random_state: Optional[np.random.RandomState] = None, block: int = 64,
-                 group=None):
+                 group=None, graph: bool = False):
         self.dev, self.mode, self.block, self.group = device_emulator, mode, int(block), group
         super().__init__(nwalkers, ndim, log_prob_fn=None, a=a, seed=seed, random_state=random_state)
         if ndim != device_emulator.d:
             raise ValueError(f"ndim {ndim} does not match the emulator's parameter dimension {device_emulator.d}")
+        self.graph = bool(graph)
+        self.n_graph_replays = 0
+        self._buf = None           # state, scratch and (with graph=True) the captured block live as long as the sampler
         self.world, self.rank = 1, 0
         try:
             import torch.distributed as dist
@@ -255,91 +263,66 @@ class DeviceStretchEnsemble(StretchEnsemble):
         self.n_log_prob_calls += 1
         self.n_log_prob_rows += n
 
-    def sample(self, initial_state: np.ndarray, iterations: int = 1, log_prob0: Optional[np.ndarray] = None):
+    # ---- random numbers of a block of steps -> the fixed device buffers ------------------------------------------------
+    def _draw(self, nb: int):
+        """Host side of a block: everything ``nb`` steps draw from emcee's stream (chain independent)."""
+        return draw_stretch_randoms(self._random, self.nwalkers, self.ndim, nb, self.a)
+
+    def _upload(self, drawn, nb: int, rd: dict) -> None:
         import torch
 
-        x0 = np.array(initial_state, dtype=np.float64, copy=True)
-        W, nd, ns = self.nwalkers, self.ndim, self.nwalkers // 2
-        if x0.shape != (W, nd):
-            raise ValueError("incompatible input dimensions")
-        check_initial_state(x0)
-        device = torch.device("cuda", self.dev.device)
-        with torch.cuda.device(device):
-            coords = torch.from_numpy(x0).to(device)
-            logp = torch.empty(W, dtype=torch.float64, device=device)
-            per = (W + self.world - 1) // self.world
-            self._send = torch.full((per,), float("nan"), dtype=torch.float64, device=device)
-            self._recv = torch.empty(per * self.world, dtype=torch.float64, device=device)
-            if log_prob0 is None:
-                self._device_log_prob(coords, logp)
-            else:
-                logp.copy_(torch.from_numpy(np.array(log_prob0, dtype=np.float64)))
-            if bool(torch.isnan(logp).any()):
-                raise ValueError("Probability function returned NaN")
-            q = torch.empty((ns, nd), dtype=torch.float64, device=device)
-            new_lp = torch.empty(ns, dtype=torch.float64, device=device)
-            n_acc = torch.zeros(W, dtype=torch.int64, device=device)
-            nan_flag = torch.zeros(1, dtype=torch.int32, device=device)
-            done = 0
-            r = draw_stretch_randoms(self._random, W, nd, min(self.block, iterations), self.a)
-            while done < iterations:
-                nb = min(self.block, iterations - done)
-                rd = {k: torch.from_numpy(v).pin_memory().to(device, non_blocking=True) for k, v in r.items()}
-                chain_b = torch.empty((nb, W, nd), dtype=torch.float64, device=device)
-                lp_b = torch.empty((nb, W), dtype=torch.float64, device=device)
-                for t in range(nb):
-                    for split in range(2):
-                        s_idx = rd["s_idx"][t, split]
-                        self.dev.stretch_propose(coords, s_idx, rd["c_idx"][t, split], rd["zz"][t, split], q)
-                        self._device_log_prob(q, new_lp)
-                        self.dev.stretch_accept(coords, logp, s_idx, q, new_lp, rd["factors"][t, split], rd["logu"][t, split],
-                                                n_acc, nan_flag)
-                    chain_b[t].copy_(coords)
-                    lp_b[t].copy_(logp)
-                if done + nb < iterations:      # the next block's random numbers are drawn while the GPU runs this one
-                    r = draw_stretch_randoms(self._random, W, nd, min(self.block, iterations - done - nb), self.a)
-                chain_h, lp_h = chain_b.cpu().numpy(), lp_b.cpu().numpy()      # synchronises: the block is done
-                if int(nan_flag.item()):
-                    raise ValueError("Probability function returned NaN")
-                self._accepted += n_acc.cpu().numpy()
-                n_acc.zero_()
-                for t in range(nb):
-                    self.iteration += 1
-                    self._chain.append(chain_h[t])
-                    self._log_prob.append(lp_h[t])
-                    yield chain_h[t], lp_h[t]
-                done += nb
+        for k, v in drawn.items():
+            rd[k][:nb].copy_(torch.from_numpy(np.ascontiguousarray(v)), non_blocking=False)
 
+    def _alloc(self, device) -> dict:
+        import torch
 
-class DevicePhiloxEnsemble(DeviceStretchEnsemble):
-    """Device-resident stretch move whose random numbers are generated on the GPU as well (SURVEY §8 f1, the variant
-    "reported separately"): counter-based Philox4x32-10 keyed by ``seed`` (``bi_stretch_randoms_philox``), fixed
-    even / odd halves instead of emcee's per-step permutation.  Nothing crosses the PCIe bus inside a block of steps, so
-    a block is a fixed launch sequence on fixed buffers and can be replayed as ONE CUDA graph (``graph=True``; single
-    process only) -- the launch-bound regime of small ensembles (100 walkers, F = 200: ~25 us kernels).
+        W, nd, ns, B = self.nwalkers, self.ndim, self.nwalkers // 2, self.block
+        f64 = dict(dtype=torch.float64, device=device)
+        per = (W + self.world - 1) // self.world
+        self._send = torch.full((per,), float("nan"), **f64)
+        self._recv = torch.empty(per * self.world, **f64)
+        rd = {k: torch.empty((B, 2, ns), dtype=torch.int32, device=device) for k in ("s_idx", "c_idx")}
+        rd.update({k: torch.empty((B, 2, ns), **f64) for k in ("zz", "factors", "logu")})
+        return dict(coords=torch.empty((W, nd), **f64), logp=torch.empty(W, **f64), q=torch.empty((ns, nd), **f64),
+                    new_lp=torch.empty(ns, **f64), n_acc=torch.zeros(W, dtype=torch.int64, device=device),
+                    nan_flag=torch.zeros(1, dtype=torch.int32, device=device), rd=rd,
+                    chain_b=torch.empty((B, W, nd), **f64), lp_b=torch.empty((B, W), **f64), graph=None)
 
-    The chain is a valid stretch-move chain but NOT emcee's for the same seed; it is reproducible from (seed, step) and
-    independent of the block size and of ``graph``.
-    """
+    def _run_block(self, nb: int) -> None:
+        bf = self._buf
+        coords, logp, q, new_lp, n_acc, nan_flag, rd = (bf[k] for k in ("coords", "logp", "q", "new_lp", "n_acc", "nan_flag", "rd"))
+        for t in range(nb):
+            for split in range(2):
+                s_idx = rd["s_idx"][t, split]
+                self.dev.stretch_propose(coords, s_idx, rd["c_idx"][t, split], rd["zz"][t, split], q)
+                self._device_log_prob(q, new_lp)
+                self.dev.stretch_accept(coords, logp, s_idx, q, new_lp, rd["factors"][t, split], rd["logu"][t, split],
+                                        n_acc, nan_flag)
+            bf["chain_b"][t].copy_(coords)
+            bf["lp_b"][t].copy_(logp)
 
-    def __init__(self, nwalkers: int, ndim: int, device_emulator, mode: str = "dense", a: float = 2.0, seed: int = 0,
-                 block: int = 64, group=None, graph: bool = False):
-        super().__init__(nwalkers, ndim, device_emulator, mode=mode, a=a, seed=0, block=block, group=group)
-        if nwalkers % 2:
-            raise ValueError("the fixed even / odd split needs an even number of walkers")
-        self.seed, self.graph, self._step = int(seed), bool(graph), 0
-        self.n_graph_replays = 0
-        self._buf = None           # state, scratch and (with graph=True) the captured block live as long as the sampler
+    def _capture(self, device) -> None:
+        """Capture ``block`` steps as one CUDA graph.  Every kernel of the block (and the communicator) has already run once
+        -- module loading and NCCL initialisation are not capturable -- and the capture itself executes nothing: the
+        state is untouched by it."""
+        import torch
 
-    def reset(self, rewind: bool = False) -> None:
-        """Forget the chain; buffers and the captured graph are kept.  The random stream carries on (burn-in and
-        production of ``mcmc.run_mcmc`` must not see the same numbers) unless ``rewind`` restarts it at step 0."""
-        super().reset()
-        if rewind:
-            self._step = 0
-
-    def _fill_randoms(self, step0: int, nb: int, rd: dict) -> None:
-        self.dev.stretch_randoms_philox(self.seed, step0, nb, self.nwalkers // 2, self.a, rd)
+        bf = self._buf
+        calls, rows = self.n_log_prob_calls, self.n_log_prob_rows
+        c2, l2, a2 = bf["coords"].clone(), bf["logp"].clone(), bf["n_acc"].clone()
+        rd = bf["rd"]
+        self.dev.stretch_propose(c2, rd["s_idx"][0, 0], rd["c_idx"][0, 0], rd["zz"][0, 0], bf["q"])      # throw-away half-step
+        self._device_log_prob(bf["q"], bf["new_lp"])
+        self.dev.stretch_accept(c2, l2, rd["s_idx"][0, 0], bf["q"], bf["new_lp"], rd["factors"][0, 0], rd["logu"][0, 0], a2,
+                                bf["nan_flag"])
+        bf["nan_flag"].zero_()
+        torch.cuda.synchronize(device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._run_block(self.block)
+        bf["graph"] = g
+        self.n_log_prob_calls, self.n_log_prob_rows = calls, rows
 
     def sample(self, initial_state: np.ndarray, iterations: int = 1, log_prob0: Optional[np.ndarray] = None):
         import torch
@@ -351,20 +334,10 @@ class DevicePhiloxEnsemble(DeviceStretchEnsemble):
         check_initial_state(x0)
         device = torch.device("cuda", self.dev.device)
         with torch.cuda.device(device):
-            f64 = dict(dtype=torch.float64, device=device)
             if self._buf is None:
-                per = (W + self.world - 1) // self.world
-                self._send = torch.full((per,), float("nan"), **f64)
-                self._recv = torch.empty(per * self.world, **f64)
-                rd = {k: torch.empty((B, 2, ns), dtype=torch.int32, device=device) for k in ("s_idx", "c_idx")}
-                rd.update({k: torch.empty((B, 2, ns), **f64) for k in ("zz", "factors", "logu")})
-                self._buf = dict(coords=torch.empty((W, nd), **f64), logp=torch.empty(W, **f64), q=torch.empty((ns, nd), **f64),
-                                 new_lp=torch.empty(ns, **f64), n_acc=torch.zeros(W, dtype=torch.int64, device=device),
-                                 nan_flag=torch.zeros(1, dtype=torch.int32, device=device), rd=rd,
-                                 chain_b=torch.empty((B, W, nd), **f64), lp_b=torch.empty((B, W), **f64), graph=None)
+                self._buf = self._alloc(device)
             bf = self._buf
-            coords, logp, q, new_lp, n_acc, nan_flag = (bf[k] for k in ("coords", "logp", "q", "new_lp", "n_acc", "nan_flag"))
-            rd, chain_b, lp_b = bf["rd"], bf["chain_b"], bf["lp_b"]
+            coords, logp, n_acc, nan_flag, rd = (bf[k] for k in ("coords", "logp", "n_acc", "nan_flag", "rd"))
             coords.copy_(torch.from_numpy(x0))
             n_acc.zero_()
             nan_flag.zero_()
@@ -374,56 +347,71 @@ class DevicePhiloxEnsemble(DeviceStretchEnsemble):
                 logp.copy_(torch.from_numpy(np.array(log_prob0, dtype=np.float64)))
             if bool(torch.isnan(logp).any()):
                 raise ValueError("Probability function returned NaN")
-
-            def run_block(nb: int) -> None:
-                for t in range(nb):
-                    for split in range(2):
-                        s_idx = rd["s_idx"][t, split]
-                        self.dev.stretch_propose(coords, s_idx, rd["c_idx"][t, split], rd["zz"][t, split], q)
-                        self._device_log_prob(q, new_lp)
-                        self.dev.stretch_accept(coords, logp, s_idx, q, new_lp, rd["factors"][t, split], rd["logu"][t, split],
-                                                n_acc, nan_flag)
-                    chain_b[t].copy_(coords)
-                    lp_b[t].copy_(logp)
-
-            if self.graph and self.world == 1 and iterations >= B and bf["graph"] is None:
-                # every kernel of the block has run once (module loading is not capturable): a throw-away half-step on copies
-                self._fill_randoms(self._step, 1, rd)
-                c2, l2, a2 = coords.clone(), logp.clone(), n_acc.clone()
-                self.dev.stretch_propose(c2, rd["s_idx"][0, 0], rd["c_idx"][0, 0], rd["zz"][0, 0], q)
-                self._device_log_prob(q, new_lp)
-                self.dev.stretch_accept(c2, l2, rd["s_idx"][0, 0], q, new_lp, rd["factors"][0, 0], rd["logu"][0, 0], a2, nan_flag)
-                nan_flag.zero_()
-                torch.cuda.synchronize(device)
-                calls, rows = self.n_log_prob_calls, self.n_log_prob_rows
-                bf["graph"] = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(bf["graph"]):
-                    run_block(B)
-                self.n_log_prob_calls, self.n_log_prob_rows = calls - 1, rows - ns      # capture and warm-up evaluate nothing kept
-            graph = bf["graph"]
             done = 0
+            drawn = self._draw(min(B, iterations))
             while done < iterations:
                 nb = min(B, iterations - done)
-                self._fill_randoms(self._step, nb, rd)
-                if graph is not None and nb == B:
-                    graph.replay()
+                self._upload(drawn, nb, rd)
+                if self.graph and nb == B and bf["graph"] is None:
+                    self._capture(device)
+                if bf["graph"] is not None and nb == B:
+                    bf["graph"].replay()
                     self.n_graph_replays += 1
                     self.n_log_prob_calls += 2 * nb
                     self.n_log_prob_rows += 2 * nb * ns
                 else:
-                    run_block(nb)
-                chain_h, lp_h = chain_b[:nb].cpu().numpy(), lp_b[:nb].cpu().numpy()      # synchronises: the block is done
+                    self._run_block(nb)
+                if done + nb < iterations:      # the next block's random numbers are drawn while the GPU runs this one
+                    drawn = self._draw(min(B, iterations - done - nb))
+                chain_h, lp_h = bf["chain_b"][:nb].cpu().numpy(), bf["lp_b"][:nb].cpu().numpy()   # synchronises: the block is done
                 if int(nan_flag.item()):
                     raise ValueError("Probability function returned NaN")
                 self._accepted += n_acc.cpu().numpy()
                 n_acc.zero_()
-                self._step += nb
+                self._after_block(nb)
                 for t in range(nb):
                     self.iteration += 1
                     self._chain.append(chain_h[t])
                     self._log_prob.append(lp_h[t])
                     yield chain_h[t], lp_h[t]
                 done += nb
+
+    def _after_block(self, nb: int) -> None:
+        pass
+
+
+class DevicePhiloxEnsemble(DeviceStretchEnsemble):
+    """Device-resident stretch move whose random numbers are generated on the GPU as well (SURVEY §8 f1, the variant
+    "reported separately"): counter-based Philox4x32-10 keyed by ``seed`` (``bi_stretch_randoms_philox``), fixed
+    even / odd halves instead of emcee's per-step permutation.  Nothing crosses the PCIe bus inside a block of steps;
+    with ``graph=True`` a block is replayed as one CUDA graph.
+
+    The chain is a valid stretch-move chain but NOT emcee's for the same seed; it is reproducible from (seed, step) and
+    independent of the block size and of ``graph``.
+    """
+
+    def __init__(self, nwalkers: int, ndim: int, device_emulator, mode: str = "dense", a: float = 2.0, seed: int = 0,
+                 block: int = 64, group=None, graph: bool = False):
+        super().__init__(nwalkers, ndim, device_emulator, mode=mode, a=a, seed=0, block=block, group=group, graph=graph)
+        if nwalkers % 2:
+            raise ValueError("the fixed even / odd split needs an even number of walkers")
+        self.seed, self._step = int(seed), 0
+
+    def reset(self, rewind: bool = False) -> None:
+        """Forget the chain; buffers and the captured graph are kept.  The random stream carries on (burn-in and
+        production of ``mcmc.run_mcmc`` must not see the same numbers) unless ``rewind`` restarts it at step 0."""
+        super().reset()
+        if rewind:
+            self._step = 0
+
+    def _draw(self, nb: int):
+        return None                      # nothing comes from the host
+
+    def _upload(self, drawn, nb: int, rd: dict) -> None:
+        self.dev.stretch_randoms_philox(self.seed, self._step, nb, self.nwalkers // 2, self.a, rd)
+
+    def _after_block(self, nb: int) -> None:
+        self._step += nb
 
 
 class BatchedClosureEnsemble:

@@ -139,8 +139,9 @@ def run_mcmc(config, closure_index: int = -1, *, emulation_config=None, emulatio
     log_posterior.initialize_pool_variables(lo, hi, emulation_config, emulation_results, experimental_results, None,
                                             sigma_exp=sigma_exp, mode=mode)
     rng = np.random.RandomState(seed)
-    if sampler == "device":
-        sampler = DeviceStretchEnsemble(config.n_walkers, ndim, log_posterior.device(), mode=mode, random_state=rng)
+    if sampler in ("device", "device_graph"):      # device_graph: blocks of steps replayed as one CUDA graph, same chain
+        sampler = DeviceStretchEnsemble(config.n_walkers, ndim, log_posterior.device(), mode=mode, random_state=rng,
+                                        graph=sampler.endswith("graph"))
     elif sampler in ("device_philox", "device_philox_graph"):      # device-side random numbers: not emcee's stream
         from .ensemble import DevicePhiloxEnsemble
         sampler = DevicePhiloxEnsemble(config.n_walkers, ndim, log_posterior.device(), mode=mode,
@@ -151,7 +152,7 @@ def run_mcmc(config, closure_index: int = -1, *, emulation_config=None, emulatio
             fn = ShardedLogProb(fn)
         sampler = StretchEnsemble(config.n_walkers, ndim, fn, random_state=rng)
     else:
-        raise ValueError("sampler must be 'device', 'host', 'device_philox' or 'device_philox_graph'")
+        raise ValueError("sampler must be 'device', 'device_graph', 'host', 'device_philox' or 'device_philox_graph'")
 
     logger.info("Initializing sampler...")
     random_pos = rng.uniform(lo, hi, (config.n_walkers, ndim))                       # mcmc.py:88

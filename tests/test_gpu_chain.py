@@ -99,6 +99,35 @@ def test_device_resident_sampler_matches_host_sampler(mode):
     assert devs.n_log_prob_rows == host.n_log_prob_rows
 
 
+def test_emcee_stream_sampler_as_cuda_graph_is_the_same_chain():
+    """graph=True on the emcee-stream sampler: blocks of steps replayed as one CUDA graph (random numbers uploaded per
+    block into fixed buffers) give the host sampler's chain bit for bit, ragged last block included."""
+    from bayesian_inference_b200.device import DeviceEmulator
+    from bayesian_inference_b200.ensemble import DeviceStretchEnsemble
+
+    z, _ = load_golden("mid")
+    W, nsteps, seed, d = 32, 150, 77, int(z["d"])
+    x0 = np.random.RandomState(3).uniform(0.1, 0.9, (W, d))
+    with DeviceEmulator(image.EmulatorImage.from_flat(z)) as dev:
+        host = StretchEnsemble(W, d, lambda X: dev.log_posterior(X, n_div=1.0), seed=seed)
+        host.run_mcmc(x0, nsteps)
+        g = DeviceStretchEnsemble(W, d, dev, seed=seed, block=32, graph=True)         # 150 = 4 x 32 + 22
+        g.run_mcmc(x0, nsteps)
+        # other divisors on the same handle between replays must not disturb the captured block (A tiles of n_div = 1 are
+        # never rewritten, ADVICE r1)
+        dev.log_posterior(x0, n_div=None)
+        dev.log_posterior(x0[:7], n_div=3.0)
+        g2 = DeviceStretchEnsemble(W, d, dev, seed=seed, block=32, graph=True)
+        g2.run_mcmc(x0, 64)
+        dev.log_posterior(x0, n_div=5.0)
+        g2.run_mcmc(g2.get_chain()[-1], 64, log_prob0=g2.get_log_prob()[-1])
+    assert g.n_graph_replays == 4
+    assert np.array_equal(g.get_chain(), host.get_chain()) and np.array_equal(g.get_log_prob(), host.get_log_prob())
+    assert np.array_equal(g.acceptance_fraction, host.acceptance_fraction)
+    assert g.n_log_prob_rows == host.n_log_prob_rows
+    assert g2.n_graph_replays == 4 and np.array_equal(g2.get_chain(), host.get_chain()[:128])
+
+
 def test_device_sampler_raises_on_nan_like_emcee():
     """A covariance that is not positive definite gives NaN; emcee raises ValueError, so does the device sampler."""
     from bayesian_inference_b200.device import DeviceEmulator
@@ -156,8 +185,8 @@ def test_philox_sampler_is_the_host_replay_and_graph_invariant():
     x0 = np.random.RandomState(3).uniform(0.1, 0.9, (W, d))
 
     class Replay(DevicePhiloxEnsemble):
-        def _fill_randoms(self, step0, nb, rd):
-            r = ph.stretch_randoms(self.seed, step0, nb, self.nwalkers, self.ndim, self.a)
+        def _upload(self, drawn, nb, rd):
+            r = ph.stretch_randoms(self.seed, self._step, nb, self.nwalkers, self.ndim, self.a)
             for k, v in r.items():
                 rd[k][:nb].copy_(torch.from_numpy(v))
 

@@ -1,5 +1,15 @@
-"""Chain throughput of mcmc-style sampling: host-side stretch move calling the CUDA log-posterior once
-per half-step vs the device-resident sampler.  python tools/chain_bench.py [--workload C1] [--steps 500] [--mode dense]"""
+"""Chain throughput of mcmc-style sampling: ONE ensemble advanced by the stretch move, proposals of every
+half-step evaluated by the CUDA log-posterior.
+
+    python tools/chain_bench.py [--workload C1] [--steps 500] [--mode dense] [--closures N]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/chain_bench.py ...
+
+Single process: host-side stretch move vs the device-resident sampler (eager and as CUDA graphs), emcee's random stream
+and the Philox variant.  Under torchrun (one rank per GPU): STRONG scaling of one ensemble -- the W/2 proposals of a
+half-step are split over the ranks and one NCCL all-gather of log-probabilities closes it (the reference's
+``pool.map`` boundary, mcmc.py:77-85); the all-gather is also timed alone (CUDA events around a loop of the same call on
+the same buffers) to give its share of a half-step.  Rank 0 prints one JSON line.
+"""
 from __future__ import annotations
 
 import argparse
@@ -21,12 +31,23 @@ def main():
     ap.add_argument("--mode", default="dense")
     ap.add_argument("--block", type=int, default=64)
     ap.add_argument("--closures", type=int, default=0, help="also run N closure chains batched (SURVEY f3)")
+    ap.add_argument("--samplers", default="", help="comma list out of host,device,device_graph,device_philox,device_philox_graph")
     a = ap.parse_args()
     import torch
 
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
     from bayesian_inference_b200 import image, synthetic
     from bayesian_inference_b200.device import DeviceEmulator
-    from bayesian_inference_b200.ensemble import DevicePhiloxEnsemble, DeviceStretchEnsemble, StretchEnsemble
+    from bayesian_inference_b200.ensemble import DevicePhiloxEnsemble, DeviceStretchEnsemble, ShardedLogProb, StretchEnsemble
 
     spec = synthetic.config(a.workload)
     if a.walkers:
@@ -36,27 +57,69 @@ def main():
                      experimental_results=an.experimental_results, sigma_exp=an.sigma_exp)
     W, d = spec.n_walkers, spec.d
     x0 = np.random.RandomState(1).uniform(0.3, 0.7, (W, d))
-    out = {"workload": spec.name, "walkers": W, "steps": a.steps, "mode": a.mode, "n_obs": img.n_features}
-    with DeviceEmulator(img, max_batch=max(W, a.closures * W)) as dev:
-        for name, mk in (("host", lambda: StretchEnsemble(W, d, lambda X: dev.log_posterior(X, n_div=1.0, mode=a.mode), seed=3)),
-                         ("device", lambda: DeviceStretchEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block)),
-                         ("device_philox", lambda: DevicePhiloxEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block)),
-                         ("device_philox_graph", lambda: DevicePhiloxEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block, graph=True))):
-            s = mk()
+    out = {"workload": spec.name, "walkers": W, "steps": a.steps, "mode": a.mode, "n_obs": img.n_features, "n_gpus": world,
+           "block": a.block, "scaling": "strong (one ensemble, proposals of a half-step split over the ranks)" if world > 1 else "single GPU"}
+    names = a.samplers.split(",") if a.samplers else (["device", "device_graph"] if world > 1 else
+                                                      ["host", "device", "device_graph", "device_philox", "device_philox_graph"])
+    with DeviceEmulator(img, device=local_rank, max_batch=max(W, a.closures * W)) as dev:
+        def host_fn(X):
+            return dev.log_posterior(X, n_div=1.0, mode=a.mode)
+
+        mk = {"host": lambda: StretchEnsemble(W, d, ShardedLogProb(host_fn) if world > 1 else host_fn, seed=3),
+              "device": lambda: DeviceStretchEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block),
+              "device_graph": lambda: DeviceStretchEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block, graph=True),
+              "device_philox": lambda: DevicePhiloxEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block),
+              "device_philox_graph": lambda: DevicePhiloxEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block, graph=True)}
+        sums = {}
+        for name in names:
+            s = mk[name]()
             s.run_mcmc(x0, max(10, a.block) if "graph" in name else 10)      # warm-up (captures the block graph)
             if "graph" in name:
-                s.reset(rewind=True)       # keeps buffers and the captured graph: steady-state replay is what is timed
+                s.reset()                  # keeps buffers and the captured graph: steady-state replay is what is timed
+                if "philox" in name:
+                    s.reset(rewind=True)
+                else:
+                    s._random = np.random.RandomState(3)
             else:
-                s = mk()
+                s = mk[name]()
             torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
             t0 = time.perf_counter()
             s.run_mcmc(x0, a.steps)
             torch.cuda.synchronize()
             dt = time.perf_counter() - t0
+            if dist is not None:
+                t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dt = float(t.item())
             out[name] = {"seconds": dt, "steps_per_s": a.steps / dt, "evals_per_s": (a.steps + 1) * W / dt,
-                         "acceptance": float(s.acceptance_fraction.mean())}
-            out[name + "_chain_sum"] = float(np.sum(s.get_chain()))
-        if a.closures:
+                         "half_step_us": dt / (2 * a.steps) * 1e6, "acceptance": float(s.acceptance_fraction.mean()),
+                         "graph_replays": getattr(s, "n_graph_replays", 0)}
+            sums[name] = float(np.sum(s.get_chain()))
+        if world > 1:
+            # the collective alone: the very call of a half-step (W/2 log-probabilities, ceil(W/2/N) per rank), CUDA events
+            per = (W // 2 + world - 1) // world
+            send = torch.zeros(per, dtype=torch.float64, device="cuda")
+            recv = torch.empty(per * world, dtype=torch.float64, device="cuda")
+            for _ in range(20):
+                dist.all_gather_into_tensor(recv, send)
+            torch.cuda.synchronize()
+            dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            n_ag = 500
+            e0.record()
+            for _ in range(n_ag):
+                dist.all_gather_into_tensor(recv, send)
+            e1.record()
+            torch.cuda.synchronize()
+            ag_us = e0.elapsed_time(e1) / n_ag * 1e3
+            t = torch.tensor([ag_us], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ag_us = float(t.item())
+            best = min((out[n]["half_step_us"] for n in names))
+            out["all_gather"] = {"bytes_per_rank": per * 8, "us_per_call_back_to_back": ag_us, "share_of_best_half_step": ag_us / best}
+        if a.closures and world == 1:
             from bayesian_inference_b200.ensemble import BatchedClosureEnsemble
 
             C_ = a.closures
@@ -73,10 +136,18 @@ def main():
             dt = time.perf_counter() - t0
             out["closures_batched"] = {"chains": C_, "seconds": dt, "chain_steps_per_s": C_ * a.steps / dt,
                                        "evals_per_s": ens.n_log_prob_rows / dt,
-                                       "speedup_vs_serial_device_chains": (C_ * a.steps / dt) / out["device"]["steps_per_s"]}
-    out["identical_chain"] = out.pop("host_chain_sum") == out.pop("device_chain_sum")
-    out["identical_chain_philox_graph"] = out.pop("device_philox_chain_sum") == out.pop("device_philox_graph_chain_sum")
-    print(json.dumps(out))
+                                       "speedup_vs_serial_device_chains": (C_ * a.steps / dt) / out["device"]["steps_per_s"]
+                                       if "device" in out else None}
+    emcee_stream = [n for n in names if "philox" not in n]
+    out["identical_chain_emcee_stream"] = len({sums[n] for n in emcee_stream}) <= 1
+    philox = [n for n in names if "philox" in n]
+    if philox:
+        out["identical_chain_philox"] = len({sums[n] for n in philox}) <= 1
+    if rank == 0:
+        print(json.dumps(out))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
