@@ -8,9 +8,11 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/bi_b200.h"
+#include "block_direct.cuh"
 #include "chol_loglik.cuh"
 #include "chol_pipe.cuh"
 #include "common.cuh"
@@ -56,6 +58,8 @@ struct bi_handle_s {
     cudaStream_t stream = nullptr;
     std::vector<GroupImg> groups;
     std::vector<void*> allocs;
+    bool guard = false;                                        // BI_DEBUG_GUARD=1: canary bands + poisoned payloads
+    std::vector<std::pair<unsigned char*, size_t>> guards;     // (base of the allocation, payload bytes)
     PcDesc* dPcs = nullptr;
     double *dMin = nullptr, *dMax = nullptr;
     std::vector<double> hMin, hMax;
@@ -64,6 +68,11 @@ struct bi_handle_s {
     double *dSig = nullptr, *dYerr = nullptr, *dATiles = nullptr, *dTmP = nullptr;
     int nTc = 0, chol_impl = 2;
     size_t pipe_smem = 0, pipe_smem_wide = 0;
+    // 4-consumer instantiation of K4 (three CTAs per SM) for few-tile problems and launches of more than two walkers per SM:
+    // -1 = choose per launch, 0 = never, 1 = always (developer knob BI_PIPE_SMALL)
+    int pipe_small = -1;
+    size_t pipe_smem_small = 0;
+    int chol_ctas_small = 0;
     int pipe_wide = 0;        // 16-consumer instantiation of K4 available (tail of a launch, launches of <= one walker per SM)
     // A tiles (Sigma_exp + blockdiag(U s s^T) / n_div) per divisor: slot 0 is n_div = 1 (what an MCMC evaluates; built
     // on its first use and never rebuilt, so a captured CUDA graph that reads it stays valid whatever else the handle is asked
@@ -89,6 +98,18 @@ struct bi_handle_s {
     double *dG = nullptr, *dH = nullptr, *dQ0 = nullptr, *dLdA = nullptr;
     double *dMw = nullptr, *dUw = nullptr, *dQuadA = nullptr, *dQuadM = nullptr, *dLdM = nullptr, *dLpW = nullptr, *dWbWs = nullptr;
     int *dInfoW = nullptr, *dWbK = nullptr;
+    // block-direct evaluation of BI_MODE_STRUCTURED (every observable block fits one warp: f_b <= 31)
+    int bd_state = 0;             // 0 not looked at yet, 1 usable, -1 not applicable (falls back to the tile-skipping kernel)
+    int bdFB = 0;
+    std::vector<BdBlock> bdBlocks;
+    BdBlock* dBdBlocks = nullptr;
+    double* dBdA[2] = {nullptr, nullptr};      // [0] n_div = 1 (never rewritten), [1] the last other divisor
+    double bd_ndiv[2] = {-1.0, -1.0};
+    double* dBdPart = nullptr;
+    int* dBdBad = nullptr;
+    double* dBdASets = nullptr;   // (n_sets, sum f_b^2): A_b per experimental data set (bi_set_data_sets)
+    double bd_sets_ndiv = -1.0;
+    long long bd_a_tot = 0;
     int *dObs = nullptr, *dTileOmin = nullptr, *dTileOmax = nullptr;
     int *dKminDense = nullptr, *dImaxDense = nullptr, *dKminStruct = nullptr, *dImaxStruct = nullptr;
     std::vector<int> hOmin, hOmax, hKmin[2], hImax[2];   // host copies of the tile tables ([0] dense, [1] structured)
@@ -101,6 +122,7 @@ struct bi_handle_s {
     long long ws_stride = 0;
     size_t chol_smem = 0, gp_smem = 0;
     int gp_wt = 32;
+    int gp_small = 1;         // 8-walker tiles for launches of less than one wave (developer knob BI_GP_SMALL=0 switches it off)
     int k3_persist = -1;      // covariance assembly: -1 = choose per layout, 0 / 1 = developer override (BI_K3_PERSIST)
     double k3_block_share = 1.0;
     double* dOutScratch = nullptr;   // staging for *_host outputs (mean / cov / k)
@@ -130,18 +152,54 @@ int fail(bi_handle h, int code, const char* msg) {
     return code;
 }
 
+// Guard mode (BI_DEBUG_GUARD=1, developer / test knob; compute-sanitizer is closed on this pool): every buffer of the
+// handle is allocated between two 4 KB canary bands and its payload is poisoned with 0xFF bytes (a NaN for doubles), so
+// that a store outside a buffer shows up in bi_query(h, 32) and a read of never-written scratch shows up as NaN in the
+// results.  No effect on the kernels themselves.
+constexpr size_t GUARD_BYTES = 4096;
+constexpr unsigned char GUARD_PATTERN = 0xA5;
+
 template <typename T>
 int dalloc(bi_handle h, T** p, size_t n) {
     void* q = nullptr;
-    cudaError_t e = cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T));
+    const size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
+    const size_t pad = h->guard ? GUARD_BYTES : 0;
+    cudaError_t e = cudaMalloc(&q, bytes + 2 * pad);
+    if (e == cudaSuccess && h->guard) {
+        // on the handle's own stream: the uploads that follow (cudaMemcpyAsync on h->stream, a non-blocking stream) must
+        // not be overtaken by the poison
+        e = cudaMemsetAsync(q, GUARD_PATTERN, bytes + 2 * pad, h->stream);
+        if (e == cudaSuccess) e = cudaMemsetAsync(static_cast<unsigned char*>(q) + pad, 0xFF, bytes, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        h->guards.push_back({static_cast<unsigned char*>(q), bytes});
+    }
     if (e != cudaSuccess) {
         h->err = std::string("cudaMalloc: ") + cudaGetErrorString(e);
         return (int)e;
     }
     h->allocs.push_back(q);
     h->scratch_bytes += n * sizeof(T);
-    *p = reinterpret_cast<T*>(q);
+    *p = reinterpret_cast<T*>(static_cast<unsigned char*>(q) + pad);
     return 0;
+}
+
+// number of canary bands that no longer hold their pattern (guard mode), -1 when guard mode is off
+int64_t check_guards(bi_handle h) {
+    if (!h->guard) return -1;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    std::vector<unsigned char> buf(GUARD_BYTES);
+    int64_t broken = 0;
+    for (auto& g : h->guards) {
+        for (int side = 0; side < 2; ++side) {
+            const unsigned char* src = side == 0 ? g.first : g.first + GUARD_BYTES + g.second;
+            if (cudaMemcpy(buf.data(), src, GUARD_BYTES, cudaMemcpyDeviceToHost) != cudaSuccess) return -2;
+            bool ok = true;
+            for (unsigned char b : buf) ok = ok && b == GUARD_PATTERN;
+            broken += !ok;
+        }
+    }
+    return broken;
 }
 
 template <typename T>
@@ -203,7 +261,9 @@ struct ProfScope {
 };
 
 int launch_gp(bi_handle h, const double* dTheta, long long W, double* dM, double* dV, cudaStream_t s) {
-    const int wt = h->gp_wt;
+    int wt = h->gp_wt;
+    // small batches (a sampler half-step of a 100-walker ensemble): fewer than one wave of 32-walker CTAs -> 8-walker tiles
+    if (wt == 32 && h->gp_small && ((W + 31) / 32) * h->Ptot < 2ll * h->sm_count) wt = 8;
     dim3 grid((unsigned)((W + wt - 1) / wt), (unsigned)h->Ptot);
     {
         ProfScope ps(h, 0, s);
@@ -212,6 +272,8 @@ int launch_gp(bi_handle h, const double* dTheta, long long W, double* dM, double
 #endif
         if (wt == 64)
             gp_predict_kernel<true, 64><<<grid, 512, h->gp_smem, s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
+        else if (wt == 8)
+            gp_predict_kernel<true, 8><<<grid, gp_threads(8), gp_smem_bytes(h->d, h->Nmax, 8), s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
         else
             gp_predict_kernel<true, 32><<<grid, 256, h->gp_smem, s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
 #ifdef GP_TIMING
@@ -272,8 +334,17 @@ int launch_chol(bi_handle h, const double* dTheta, const double* dM, const doubl
             const long long w_main = W - w_tail;
             if (w_main > 0) {
                 PP.c.W = w_main;
-                chol_pipe_kernel<PIPE_CONSUMERS_MAIN><<<(int)std::min<long long>(w_main, h->chol_ctas), pipe_threads(PIPE_CONSUMERS_MAIN),
-                                                        h->pipe_smem, s>>>(PP);
+                // few tiles (F <= 287): a walker's time is the chain potrf -> solve -> next diagonal tile, so with more than
+                // two walkers per SM on offer a third CTA per SM (4 consumers each) beats wider rounds: C1 shapes, 1200
+                // walkers 0.489 -> 0.408 ms; 100 walkers 0.093 -> 0.100 ms (profiles/r02_notes.md).  Same arithmetic per strip.
+                const bool small = h->chol_ctas_small > 0 &&
+                                   (h->pipe_small == 1 || (h->pipe_small < 0 && h->nt < 10 && w_main > 2ll * h->sm_count));
+                if (small)
+                    chol_pipe_kernel<PIPE_CONSUMERS_SMALL><<<(int)std::min<long long>(w_main, h->chol_ctas_small),
+                                                             pipe_threads(PIPE_CONSUMERS_SMALL), h->pipe_smem_small, s>>>(PP);
+                else
+                    chol_pipe_kernel<PIPE_CONSUMERS_MAIN><<<(int)std::min<long long>(w_main, h->chol_ctas),
+                                                            pipe_threads(PIPE_CONSUMERS_MAIN), h->pipe_smem, s>>>(PP);
             }
             if (w_tail > 0) {
                 PipeParams PT = PP;
@@ -361,9 +432,17 @@ static int64_t k4_dmma_per_walker(bi_handle h, int mode) {
     return n;
 }
 
+static int ensure_block_direct(bi_handle h);
+
 int64_t bi_query(bi_handle h, int what) {
     if (!h) return -1;
     if (what == 16 || what == 17) return k4_dmma_per_walker(h, what - 16);
+    if (what == 32) return check_guards(h);
+    if (what == 18) {
+        if (!h->has_data || !h->sigma_blockdiag) return 0;
+        cudaSetDevice(h->device);
+        return (ensure_block_direct(h) == 0 && h->bd_state == 1) ? 1 : 0;
+    }
     switch (what) {
         case 0: return h->F;
         case 1: return h->Ptot;
@@ -415,6 +494,7 @@ void bi_destroy(bi_handle h) {
     if (h->dEsets) cudaFree(h->dEsets);
     if (h->dYerrSets) cudaFree(h->dYerrSets);
     if (h->dATilesSets) cudaFree(h->dATilesSets);
+    if (h->dBdASets) cudaFree(h->dBdASets);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -427,6 +507,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         !D->prior_min || !D->prior_max)
         return BI_E_ARG;
     bi_handle h = new bi_handle_s();
+    if (const char* e = std::getenv("BI_DEBUG_GUARD")) h->guard = std::atoi(e) != 0;
     auto bail = [&](int rc) {
         std::fprintf(stderr, "bi_create failed (%d): %s\n", rc, h->err.c_str());
         bi_destroy(h);
@@ -697,6 +778,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
 
     h->gp_wt = 32;   // measured (C3, B200): 32 walkers x 2 CTAs/SM 0.124 ms, 64 walkers x 1 CTA/SM 0.138 ms per 1024 walkers
     if (const char* e = std::getenv("BI_GP_WT")) h->gp_wt = std::atoi(e) == 64 ? 64 : 32;   // developer A/B knob
+    if (const char* e = std::getenv("BI_GP_SMALL")) h->gp_small = std::atoi(e) != 0;
     if (gp_smem_bytes(d, h->Nmax, h->gp_wt) > 227 * 1024) h->gp_wt = 32;
     h->gp_smem = gp_smem_bytes(d, h->Nmax, h->gp_wt);
     if (h->gp_smem > 227 * 1024) {
@@ -709,6 +791,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
     } else {
         CKB(allow_max_smem(gp_predict_kernel<true, 32>));
         CKB(allow_max_smem(gp_predict_kernel<false, 32>));
+        CKB(allow_max_smem(gp_predict_kernel<true, 8>));
     }
     CKB(allow_max_smem(cov_persist_kernel));
     if (const char* e = std::getenv("BI_K3_PERSIST")) h->k3_persist = std::atoi(e) != 0;   // developer A/B knob
@@ -726,12 +809,21 @@ int bi_create(const bi_desc* D, bi_handle* out) {
             return bail(BI_E_UNSUPPORTED);
         }
         if (const char* e = std::getenv("BI_CHOL_IMPL")) h->chol_impl = std::atoi(e) == 1 ? 1 : 2;
+        if (const char* e = std::getenv("BI_PIPE_SMALL")) h->pipe_small = std::atoi(e) != 0;   // developer A/B knob
         h->pipe_smem = pipe_smem_bytes(Fp, h->nTc * 32);
         if (h->chol_impl == 2 && (h->pipe_smem > 227 * 1024 || nt > 120)) h->chol_impl = 1;
         if (h->chol_impl == 2) {
             CKB(allow_max_smem(chol_pipe_kernel<PIPE_CONSUMERS_MAIN>));
             CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_pipe_kernel<PIPE_CONSUMERS_MAIN>, pipe_threads(PIPE_CONSUMERS_MAIN),
                                                               h->pipe_smem));
+            if (h->pipe_small != 0) {
+                int occ_s = 0;
+                h->pipe_smem_small = pipe_smem_bytes(Fp, h->nTc * 32, PIPE_CONSUMERS_SMALL);
+                CKB(allow_max_smem(chol_pipe_kernel<PIPE_CONSUMERS_SMALL>));
+                CKB(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_s, chol_pipe_kernel<PIPE_CONSUMERS_SMALL>,
+                                                                  pipe_threads(PIPE_CONSUMERS_SMALL), h->pipe_smem_small));
+                h->chol_ctas_small = (nt < 10 || h->pipe_small == 1) ? h->sm_count * occ_s : 0;   // scratch is sized by it
+            }
             h->pipe_smem_wide = pipe_smem_bytes(Fp, h->nTc * 32, PIPE_CONSUMERS_WIDE);
             h->pipe_wide = h->pipe_smem_wide <= 227 * 1024;
             if (const char* e = std::getenv("BI_PIPE_WIDE")) { if (std::atoi(e) == 0) h->pipe_wide = 0; }   // developer A/B knob
@@ -745,7 +837,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
         if (const char* e = std::getenv("BI_CHOL_OCC")) occ = std::max(1, std::min(occ, std::atoi(e)));   // developer A/B knob
         h->chol_ctas = h->sm_count * occ;
         h->ws_stride = chol_ws_doubles(nt);
-        TRY(dalloc(h, &h->dWs, (size_t)h->chol_ctas * h->ws_stride));
+        TRY(dalloc(h, &h->dWs, (size_t)std::max(h->chol_ctas, h->chol_ctas_small) * h->ws_stride));
     }
     CKB(cudaStreamSynchronize(h->stream));
     *out = h;
@@ -1025,6 +1117,95 @@ static int run_woodbury(bi_handle h, const double* dTheta, long long W, double n
     return 0;
 }
 
+// ---- block-direct structured mode ---------------------------------------------------------------------------------------
+// BI_MODE_STRUCTURED is evaluated observable block by observable block in registers (block_direct.cuh) when every block
+// has at most 31 rows and its group at most BD_PMAX principal components; otherwise (or with BI_STRUCT_IMPL=tiles, the
+// developer A/B knob) by the fused Cholesky kernel skipping structurally-zero tiles.
+static int ensure_block_direct(bi_handle h) {
+    if (h->bd_state != 0) return 0;
+    h->bd_state = -1;
+    if (const char* e = std::getenv("BI_STRUCT_IMPL")) { if (std::string(e) == "tiles") return 0; }
+    const int nB = (int)h->blk.size();
+    int fmax = 0;
+    long long a_tot = 0;
+    h->bdBlocks.resize(nB);
+    for (int b = 0; b < nB; ++b) {
+        const GroupImg& I = h->groups[h->blk[b][0]];
+        BdBlock& B = h->bdBlocks[b];
+        B.row0 = (int)h->blk[b][1]; B.f = (int)h->blk[b][3]; B.col0 = I.pc_off; B.P = I.P; B.a_off = a_tot;
+        a_tot += (long long)B.f * B.f;
+        fmax = std::max(fmax, B.f);
+        if (B.f > 31 || B.P > BD_PMAX) return 0;
+    }
+    h->bdFB = (fmax + 7) / 8 * 8;
+    h->bd_a_tot = a_tot;
+    int rc = upload(h, &h->dBdBlocks, h->bdBlocks.data(), h->bdBlocks.size());
+    if (rc) return rc;
+    for (int i = 0; i < 2; ++i)
+        if ((rc = dalloc(h, &h->dBdA[i], (size_t)a_tot))) return rc;
+    if ((rc = dalloc(h, &h->dBdPart, (size_t)h->max_batch * nB))) return rc;
+    if ((rc = dalloc(h, &h->dBdBad, (size_t)h->max_batch * nB))) return rc;
+    CK(cudaStreamSynchronize(h->stream));
+    h->bd_state = 1;
+    return 0;
+}
+
+static int run_block_direct(bi_handle h, const double* dTheta, long long W, double n_div, double* dLogp, int* dInfo, cudaStream_t s,
+                            const int* dSetId = nullptr) {
+    const int nB = (int)h->bdBlocks.size();
+    const int slot = (n_div == 1.0) ? 0 : 1;
+    const double *dAall = h->dBdA[slot], *dEall = h->dE;
+    long long e_stride = 0, a_stride = 0;
+    if (dSetId) {
+        if (!h->dBdASets) CK(cudaMalloc(&h->dBdASets, (size_t)h->n_sets * h->bd_a_tot * 8));
+        if (h->bd_sets_ndiv != n_div) {
+            for (int c = 0; c < h->n_sets; ++c) {
+                block_a_kernel<<<nB, 256, 0, s>>>(h->dBdBlocks, h->F, nullptr, h->dYerrSets + (size_t)c * h->F, h->dUblk, n_div,
+                                                  h->dBdASets + (size_t)c * h->bd_a_tot);
+                h->launches++;
+            }
+            CK(cudaGetLastError());
+            h->bd_sets_ndiv = n_div;
+        }
+        dAall = h->dBdASets; dEall = h->dEsets; e_stride = h->Fp; a_stride = h->bd_a_tot;
+    } else if (h->bd_ndiv[slot] != n_div) {
+        block_a_kernel<<<nB, 256, 0, s>>>(h->dBdBlocks, h->F, h->dSig, h->dYerr, h->dUblk, n_div, h->dBdA[slot]);
+        h->launches++;
+        CK(cudaGetLastError());
+        h->bd_ndiv[slot] = n_div;
+    }
+    const size_t smem = block_direct_smem_bytes(h->bdFB);
+    for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
+        const long long wb = std::min<long long>(h->max_batch, W - w0);
+        int rc = launch_gp(h, dTheta + w0 * h->d, wb, h->dM, h->dV, s);
+        if (rc) return rc;
+        // walkers per warp: enough (walker, block) tasks per launch to fill the machine a few times over, at most 8
+        const long long tasks = wb * nB;
+        int wpw = (int)std::max<long long>(1, std::min<long long>(8, tasks / ((long long)h->sm_count * 2 * BD_WARPS * 4)));
+        const dim3 grid((unsigned)nB, (unsigned)((wb + (long long)BD_WARPS * wpw - 1) / ((long long)BD_WARPS * wpw)));
+        {
+            ProfScope ps(h, 1, s);
+#define BD_LAUNCH(FBV)                                                                                                       \
+    block_direct_kernel<FBV><<<grid, BD_THREADS, smem, s>>>(h->dBdBlocks, nB, wb, wpw, h->Ptot, h->K0, h->dM, h->dV, h->dTrow, dEall, \
+                                                            dAall, h->dBdPart, h->dBdBad, dSetId ? dSetId + w0 : nullptr, e_stride,  \
+                                                            a_stride)
+            switch (h->bdFB) {
+                case 8: BD_LAUNCH(8); break;
+                case 16: BD_LAUNCH(16); break;
+                case 24: BD_LAUNCH(24); break;
+                default: BD_LAUNCH(32); break;
+            }
+#undef BD_LAUNCH
+            block_combine_kernel<<<(unsigned)((wb + 127) / 128), 128, 0, s>>>(nB, wb, h->d, dTheta + w0 * h->d, h->dMin, h->dMax,
+                                                                              h->dBdPart, h->dBdBad, dLogp + w0,
+                                                                              dInfo ? dInfo + w0 : nullptr);
+        }
+        h->launches += 2;
+        CK(cudaGetLastError());
+    }
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 static int check_lp(bi_handle h, const double* theta, int64_t W, int mode, double* logp_out) {
     if (!h || !theta || !logp_out || W < 0) return fail(h, BI_E_ARG, "bad argument");
@@ -1053,6 +1234,10 @@ int bi_log_posterior(bi_handle h, const double* theta, int64_t W, double n_div, 
         n_div = cnt > 0 ? (double)cnt : 1.0;
     }
     if (mode == BI_MODE_WOODBURY) return run_woodbury(h, theta, W, n_div, logp_out, info_out, s);
+    if (mode == BI_MODE_STRUCTURED) {
+        if ((rc = ensure_block_direct(h))) return rc;
+        if (h->bd_state == 1) return run_block_direct(h, theta, W, n_div, logp_out, info_out, s);
+    }
     rc = build_a_tiles(h, n_div, s);
     if (rc) return rc;
     for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
@@ -1083,7 +1268,12 @@ int bi_log_posterior_host(bi_handle h, const double* theta, int64_t W, double n_
         }
         n_div = cnt > 0 ? (double)cnt : 1.0;
     }
-    if (mode != BI_MODE_WOODBURY) {
+    bool direct = false;
+    if (mode == BI_MODE_STRUCTURED) {
+        if ((rc = ensure_block_direct(h))) return rc;
+        direct = h->bd_state == 1;
+    }
+    if (mode != BI_MODE_WOODBURY && !direct) {
         rc = build_a_tiles(h, n_div, h->stream);
         if (rc) return rc;
     }
@@ -1092,6 +1282,9 @@ int bi_log_posterior_host(bi_handle h, const double* theta, int64_t W, double n_
         CK(cudaMemcpyAsync(h->dTheta, theta + w0 * h->d, (size_t)wb * h->d * 8, cudaMemcpyHostToDevice, h->stream));
         if (mode == BI_MODE_WOODBURY) {
             rc = run_woodbury(h, h->dTheta, wb, n_div, h->dLogp, h->dInfo, h->stream);
+            if (rc) return rc;
+        } else if (direct) {
+            rc = run_block_direct(h, h->dTheta, wb, n_div, h->dLogp, h->dInfo, h->stream);
             if (rc) return rc;
         } else {
             rc = launch_gp(h, h->dTheta, wb, h->dM, h->dV, h->stream);
@@ -1200,8 +1393,9 @@ int bi_set_data_sets(bi_handle h, int32_t n_sets, const double* y, const double*
     if (!h->has_data) return fail(h, BI_E_STATE, "handle was created without experimental data (scratch is sized by it)");
     CK(cudaSetDevice(h->device));
     CK(cudaDeviceSynchronize());          // earlier calls may still read the previous sets on a caller's stream
-    for (double** p : {&h->dEsets, &h->dYerrSets, &h->dATilesSets})
+    for (double** p : {&h->dEsets, &h->dYerrSets, &h->dATilesSets, &h->dBdASets})
         if (*p) { cudaFree(*p); *p = nullptr; }
+    h->bd_sets_ndiv = -1.0;
     const int F = h->F, Fp = h->Fp;
     std::vector<double> e((size_t)n_sets * Fp, 0.0);
     for (int c = 0; c < n_sets; ++c)
@@ -1227,6 +1421,12 @@ int bi_log_posterior_sets(bi_handle h, const double* theta, const int32_t* set_i
     if (W == 0) return 0;
     CK(cudaSetDevice(h->device));
     cudaStream_t s = (cudaStream_t)stream;
+    if (mode == BI_MODE_STRUCTURED) {
+        if (!h->sigma_blockdiag) return fail(h, BI_E_STRUCTURE, "Sigma_exp couples observable blocks: structured mode is not valid");
+        int rc = ensure_block_direct(h);
+        if (rc) return rc;
+        if (h->bd_state == 1) return run_block_direct(h, theta, W, n_div, logp_out, info_out, s, set_id);
+    }
     if (h->sets_ndiv != n_div) {
         const int ntl = h->nt * (h->nt + 1) / 2;
         for (int c = 0; c < h->n_sets; ++c) {

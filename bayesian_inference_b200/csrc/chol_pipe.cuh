@@ -36,6 +36,10 @@ namespace bi {
 // wave and for launches of at most one walker per SM, where latency is what counts).
 constexpr int PIPE_CONSUMERS_MAIN = 8;
 constexpr int PIPE_CONSUMERS_WIDE = 16;
+// 4 consumers, three CTAs per SM: for few-tile problems (F <= ~320), where a panel has at most a dozen strips and the
+// walker's time is the chain potrf -> solve -> next diagonal tile, a third walker in flight per SM is worth more than wider
+// rounds (measured on the C1 shape, profiles/r02_notes.md).
+constexpr int PIPE_CONSUMERS_SMALL = 4;
 __host__ __device__ constexpr int pipe_threads(int nc) { return (nc + 2) * 32; }   // + producer + factor warp
 #ifndef PIPE_NSTAGES
 #define PIPE_NSTAGES 4   // measured: 3, 4, 6 and 8 stages all leave the consumers' wait at 25-30 % -- the ring is not latency bound
@@ -340,7 +344,8 @@ __device__ __forceinline__ void strip_trsm_blocked(double (&c)[2][4][2], double 
 // Row F lives in strip hA of the last row tile.  With structured skipping that strip is the only dense one: in panels
 // that do not couple to the last tile it is swept as a single extra unit, and it always starts at the panel's own kmin.
 template <int NC>
-__global__ void __launch_bounds__(pipe_threads(NC), NC == PIPE_CONSUMERS_MAIN ? 2 : 1) chol_pipe_kernel(const PipeParams PP) {
+__global__ void __launch_bounds__(pipe_threads(NC), NC == PIPE_CONSUMERS_MAIN ? 2 : (NC == PIPE_CONSUMERS_SMALL ? 3 : 1))
+chol_pipe_kernel(const PipeParams PP) {
     constexpr int PIPE_CONSUMERS = NC, PIPE_THREADS = pipe_threads(NC), STAGE_ELEMS = pipe_stage_elems(NC);
     const CholParams& P = PP.c;
     extern __shared__ __align__(16) unsigned char smem_raw[];

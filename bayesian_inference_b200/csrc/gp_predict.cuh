@@ -44,6 +44,11 @@ __device__ unsigned long long gp_dbg[8];   // developer timing: cycles of thread
 // shared FP64 pipe) or 64 (512 threads, one CTA per SM).  In-kernel clock64 timing on C3: K1 28.6 k + K2 23.6 k cycles
 // per 32-walker CTA with a co-resident CTA, K1 18.8 k + K2 39.0 k per 64-walker CTA alone; 32 x 2 wins (0.124 vs 0.138 ms).
 constexpr int GP_WT_MAX = 64;
+// A third instantiation, 8 walkers per CTA (256 threads, 32 per walker in K1, one 8-row fragment per warp in K2), is the
+// LATENCY configuration for small batches (the W/2 proposals of a sampler half-step): it spreads 50 walkers x 30 PCs over
+// 210 CTAs instead of 60, and a CTA's K1 + K2 take a quarter of the time.  Same arithmetic per element and the same
+// summation order, hence bit-identical (m, v).
+__host__ __device__ constexpr int gp_threads(int wt) { return wt >= 32 ? wt * 8 : 256; }
 
 __host__ __device__ inline size_t gp_smem_bytes(int d, int Nmax, int GP_WT) {
     const int nks = ((Nmax + 15) / 16) * 4;   // K steps, padded to whole groups of 4
@@ -141,21 +146,21 @@ __device__ __forceinline__ double stationary_kernel(double sq) {
 
 // K1 for one (walker tile, PC): thread = (walker tid/8, design points tid%8 + 8u + 32i), four design points at a time
 // so that four independent sqrt/exp dependency chains interleave.
-template <bool DO_GP, int KIND>
+template <bool DO_GP, int KIND, int TPW>
 __device__ __forceinline__ void gp_k1_loop(double* sA, const double* sX, const double* sTh, const PcDesc& pc, int d, int nks,
                                            long long w0, long long W, double* __restrict__ k_out, int k_npc, int tid) {
     const int N = pc.N;
-    const int wl = tid >> 3, jl = tid & 7;
+    const int wl = tid / TPW, jl = tid % TPW;      // TPW threads per walker (8, or 32 in the 8-walker instantiation)
     const double* th = sTh + wl * d;
     double* krow = (k_out != nullptr && w0 + wl < W) ? k_out + ((w0 + wl) * k_npc + pc.local) * N : nullptr;
-    // of_index(wl, jl + 8u + 32i, nks) = base + 64 u + 256 i
+    // of_index(wl, jl + TPW u + 4 TPW i, nks) = base + 8 TPW u + 32 TPW i
     double* sArow = sA + ((((wl >> 3) * nks + (jl >> 2)) << 5) + ((wl & 7) << 2) + (jl & 3));
     const double cst = pc.cst;
-    for (int jb = jl; jb < N; jb += 32, sArow += 256) {
+    for (int jb = jl; jb < N; jb += 4 * TPW, sArow += 32 * TPW) {
         double sq[4] = {0.0, 0.0, 0.0, 0.0};
         const double* xj[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) xj[u] = sX + min(jb + 8 * u, N - 1);
+        for (int u = 0; u < 4; ++u) xj[u] = sX + min(jb + TPW * u, N - 1);
         for (int k = 0; k < d; ++k) {
             const double tk = th[k];
 #pragma unroll
@@ -169,9 +174,9 @@ __device__ __forceinline__ void gp_k1_loop(double* sA, const double* sX, const d
         for (int u = 0; u < 4; ++u) kv[u] = stationary_kernel<KIND>(sq[u]) + cst;
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            if (jb + 8 * u < N) {
-                if (DO_GP) sArow[64 * u] = kv[u];
-                if (krow != nullptr) krow[jb + 8 * u] = kv[u];
+            if (jb + TPW * u < N) {
+                if (DO_GP) sArow[8 * TPW * u] = kv[u];
+                if (krow != nullptr) krow[jb + TPW * u] = kv[u];
             }
         }
     }
@@ -191,7 +196,8 @@ constexpr int GP_K2_OWNERS = 16 / GP_K2_NF;   // fragment-group owners per 32 wa
 
 template <int GP_WT>
 __device__ __forceinline__ void gp_k2_tile(const PcDesc& pc, const double* sA, int warp, int lane, double* sSq, double* sMn) {
-    constexpr int NF = GP_K2_NF, MI = 8 / NF, NO = GP_K2_OWNERS;
+    constexpr int NF = GP_K2_NF, NO = GP_K2_OWNERS;
+    constexpr int MI = (GP_WT >= 32) ? 8 / NF : GP_WT / 8;   // m-fragments (8 walkers each) per warp: 4, or 1 in the 8-walker tile
     constexpr int WM = GP_WT / (8 * MI);    // warps along the walker rows
     const int N = pc.N, nks = pc.nks;
     // warp (wm, wn): walker rows wm*8*MI.., fragment groups {q : snake(q) == wn}.  The B operand is cut into n-fragments
@@ -343,7 +349,7 @@ __device__ __forceinline__ void gp_finish_tile(const PcDesc& pc, const double* s
 // k_out (optional): (W, k_ld_pc, N) row-major slice for this group, PC index = desc.local.
 // m_out / v_out (optional): (W, Ptot) at column blockIdx.y + pc_first.
 template <bool DO_GP, int GP_WT>
-__global__ void __launch_bounds__(GP_WT * 8, GP_WT == 32 ? 2 : 1) gp_predict_kernel(const PcDesc* __restrict__ pcs, int pc_first, int d,
+__global__ void __launch_bounds__(gp_threads(GP_WT), GP_WT <= 32 ? 2 : 1) gp_predict_kernel(const PcDesc* __restrict__ pcs, int pc_first, int d,
                                                                 const double* __restrict__ theta, long long W,
                                                                 double* __restrict__ k_out, int k_npc,
                                                                 double* __restrict__ m_out, double* __restrict__ v_out,
@@ -357,7 +363,7 @@ __global__ void __launch_bounds__(GP_WT * 8, GP_WT == 32 ? 2 : 1) gp_predict_ker
     double* sSq = sTh + GP_WT * d;
     double* sMn = sSq + GP_WT * 8;
 
-    constexpr int GP_THREADS = GP_WT * 8;
+    constexpr int GP_THREADS = gp_threads(GP_WT), TPW = GP_THREADS / GP_WT;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long w0 = (long long)blockIdx.x * GP_WT;
 #ifdef GP_TIMING
@@ -383,10 +389,10 @@ __global__ void __launch_bounds__(GP_WT * 8, GP_WT == 32 ? 2 : 1) gp_predict_ker
 
     // ---- K1 -------------------------------------------------------------------------------------------------
     switch (pc.kind) {   // the kernel kind is a template parameter of the loop so that its four chains interleave
-        case 0: gp_k1_loop<DO_GP, 0>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
-        case 1: gp_k1_loop<DO_GP, 1>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
-        case 2: gp_k1_loop<DO_GP, 2>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
-        default: gp_k1_loop<DO_GP, 3>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
+        case 0: gp_k1_loop<DO_GP, 0, TPW>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
+        case 1: gp_k1_loop<DO_GP, 1, TPW>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
+        case 2: gp_k1_loop<DO_GP, 2, TPW>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
+        default: gp_k1_loop<DO_GP, 3, TPW>(sA, sX, sTh, pc, d, nks, w0, W, k_out, k_npc, tid); break;
     }
     if (!DO_GP) return;
     GP_T(1);

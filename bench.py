@@ -287,7 +287,11 @@ def roofline_record(img, spec_name, W, mode, dev, gp, ch, total_ms, traffic):
     else:
         achieved = fl5 * W / (ch_avg * 1e-3) / 1e12 if ch_n else None
         dmma = dev.query(17) if mode == "structured" else -1
-        rec.update(kernel=("chol_pipe_kernel with tile skipping (K5 structured)" if mode == "structured"
+        direct = mode == "structured" and dev.query(18) == 1
+        if direct:
+            dmma = -1
+        rec.update(kernel=("block_direct_kernel (K5: one warp per (walker, observable block), Cholesky in registers)" if direct
+                           else "chol_pipe_kernel with tile skipping (K5 structured)" if mode == "structured"
                            else "chol_loglik_kernel<explicit> on the P x P Woodbury matrices (K5)"),
                    achieved=achieved, frac=(achieved / FP64_TENSOR_PEAK_TFLOPS) if achieved else None, flops_per_eval=fl5,
                    flops_counting="K5: sum_b min(f_b^3/3 + f_b^2 P, P^3/3 + 3 P^2) (SURVEY 8d)",

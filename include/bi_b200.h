@@ -110,7 +110,11 @@ const char* bi_last_error(bi_handle h);
 /* query: what = 0 F, 1 total n_pc, 2 d, 3 n_groups, 4 SM count, 5 Cholesky CTAs resident, 6 scratch bytes,
  *        7 kernels launched since create (launch counter used by bench.py's gpu_launches),
  *        16 / 17 FP64 tensor instructions (DMMA m8n8k4 = 512 flop each) the fused Cholesky kernel issues per walker in
- *        BI_MODE_DENSE / BI_MODE_STRUCTURED, counted from the tile tables the kernel walks (bench.py's flops_executed) */
+ *        BI_MODE_DENSE / BI_MODE_STRUCTURED, counted from the tile tables the kernel walks (bench.py's flops_executed),
+ *        18 whether BI_MODE_STRUCTURED runs block by block in registers (1: every observable block has <= 31 rows) or on
+ *        the fused Cholesky kernel with tile skipping (0),
+ *        32 guard mode (environment BI_DEBUG_GUARD=1 at bi_create: canary bands around every device buffer of the handle,
+ *        payloads poisoned with NaN): number of canary bands overwritten so far, -1 when guard mode is off             */
 int64_t bi_query(bi_handle h, int what);
 /* synchronise the handle's own stream */
 int  bi_sync(bi_handle h);

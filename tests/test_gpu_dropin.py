@@ -136,11 +136,11 @@ def test_batched_closure_tests_equal_separate_runs(toy, tmp_path):
             assert rel_err(got[sid == c][fin], want[fin]) < 1e-9, (mode, c)
             last_x, last_lp = batched[c]["chain"][-1], batched[c]["log_prob"][-1]
             assert rel_err(last_lp, cf.log_posterior(z_c, last_x, n_div=1.0)) < 1e-9, (mode, c)
-    # the data-set entry point itself against one handle per data set
-    for c, p in enumerate(pseudo):
-        lp.initialize_pool_variables(toy.min, toy.max, toy.emulation_config, toy.emulation_results, p, None)
-        want = lp.log_posterior_walkers(th[sid == c])
-        assert np.array_equal(got[sid == c], want, equal_nan=True)
+        # the data-set entry point itself against one handle per data set, same mode: bit for bit
+        for c, p in enumerate(pseudo):
+            lp.initialize_pool_variables(toy.min, toy.max, toy.emulation_config, toy.emulation_results, p, None, mode=mode)
+            want = lp.log_posterior_walkers(th[sid == c])
+            assert np.array_equal(got[sid == c], want, equal_nan=True), (mode, c)
     lp.close()
     emulation.clear_cache()
 

@@ -143,6 +143,60 @@ def test_log_posterior_every_tile_alignment(n_obs, n_bins):
         assert np.array_equal(cov == 0.0, co == 0.0)
 
 
+# ---- structured mode: block by block in registers (f_b <= 31) vs the tile-skipping kernel vs dense vs the oracle --------
+@pytest.mark.parametrize("name,W,over", [("C4", 301, {"oob_fraction": 0.1}), ("C1", 100, {}), ("C3A", 257, {"oob_fraction": 0.02})])
+def test_structured_block_direct_equals_tile_skipping_dense_and_oracle(name, W, over, monkeypatch):
+    """SURVEY Appendix A (structured variant, f_b <= P: direct f_b x f_b Cholesky per observable block).  The block-direct
+    kernel, the fused kernel with tile skipping (forced by BI_STRUCT_IMPL=tiles) and the dense factorisation give the same
+    log-posterior; 24 rows are compared with the oracle's block-wise restatement and with its dense evaluation."""
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    a = synthetic.generate(name, n_walkers=W, **over)
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max,
+                     experimental_results=a.experimental_results)
+    z = img.to_flat()
+    with DeviceEmulator(img, max_batch=128) as dev:                      # several chunks, the last one ragged
+        assert dev.query(18) == 1
+        direct = dev.log_posterior(a.theta, n_div=1.0, mode="structured")
+        direct_nd, info = dev.log_posterior(a.theta, n_div=None, mode="structured", return_info=True)
+        dense = dev.log_posterior(a.theta, n_div=1.0, mode="dense")
+        dense_nd = dev.log_posterior(a.theta, n_div=None, mode="dense")
+        one = np.array([dev.log_posterior(a.theta[i], n_div=1.0, mode="structured")[0] for i in (0, 5, W - 1)])
+        again = dev.log_posterior(a.theta, n_div=1.0, mode="structured")
+    monkeypatch.setenv("BI_STRUCT_IMPL", "tiles")
+    with DeviceEmulator(img, max_batch=128) as dev2:
+        assert dev2.query(18) == 0
+        tiles = dev2.log_posterior(a.theta, n_div=1.0, mode="structured")
+    assert np.array_equal(direct, again, equal_nan=True)                 # deterministic (block terms summed in block order)
+    assert np.array_equal(one, direct[[0, 5, W - 1]])                    # a walker's value does not depend on its batch
+    inside = np.all((a.theta > a.min) & (a.theta < a.max), axis=1)
+    assert np.array_equal(np.isneginf(direct), ~inside) and np.array_equal(info == -1, ~inside) and np.all(info[inside] == 0)
+    for got, ref in ((direct, dense), (tiles, dense), (direct_nd, dense_nd)):
+        assert np.array_equal(np.isneginf(got), np.isneginf(ref))
+        assert rel_err(got[inside], ref[inside]) < TOL_LOGP
+    idx = np.flatnonzero(inside)[:24]
+    _cmp_logp(direct[idx], cf.log_posterior_blockwise(z, a.theta[idx], n_div=1.0))
+    _cmp_logp(direct[idx], cf.log_posterior(z, a.theta[idx], n_div=1.0))
+
+
+def test_structured_block_direct_reports_a_non_positive_definite_block():
+    """A covariance that is not positive definite gives NaN and info = the 1-based merged row of the first bad pivot, as on
+    the dense path (the reference ends in NaN too)."""
+    z, ref = load_golden("toy")
+    z = dict(z)
+    z["y_err"] = np.zeros_like(z["y_err"])
+    F = int(z["n_features"])
+    bad = -5.0 * np.eye(F)
+    z["sigma_exp"] = bad                                                  # block diagonal (diagonal) but negative
+    with _dev(z) as dev:
+        assert dev.query(18) == 1
+        th = ref["theta"][np.all((ref["theta"] > z["min"]) & (ref["theta"] < z["max"]), axis=1)][:4]
+        s, info_s = dev.log_posterior(th, n_div=1.0, mode="structured", return_info=True)
+        d, info_d = dev.log_posterior(th, n_div=1.0, mode="dense", return_info=True)
+    assert np.all(np.isnan(s)) and np.all(np.isnan(d))
+    assert np.all(info_s >= 1) and np.array_equal(info_s, info_d)
+
+
 # ---- size-independent properties at the full BASELINE size ----------------------------------------------------------
 @pytest.fixture(scope="module")
 def c3a():
@@ -297,6 +351,35 @@ def test_wave_tail_instantiation_equals_main_instantiation(c3a):
             continue
         assert np.array_equal(dev.log_posterior(a.theta[:W], n_div=1.0), full[:W]), W
         assert np.array_equal(dev.log_posterior(a.theta[-W:], n_div=1.0), full[-W:]), W
+
+
+def test_few_tile_instantiation_equals_main_instantiation(monkeypatch):
+    # few-tile problems (F <= 287) with more than two walkers per SM on offer run K4 with 4 consumers per CTA and three CTAs
+    # per SM instead of 8 and two: the same arithmetic per strip, so the values are bit-identical on both sides of the
+    # switch point, for either forced choice (BI_PIPE_SMALL), and equal to the oracle
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    a = synthetic.generate("C1", n_walkers=700, oob_fraction=0.02)
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max,
+                     experimental_results=a.experimental_results)
+    out = {}
+    for flag in (None, "0", "1"):
+        if flag is None:
+            monkeypatch.delenv("BI_PIPE_SMALL", raising=False)
+        else:
+            monkeypatch.setenv("BI_PIPE_SMALL", flag)
+        with DeviceEmulator(img, max_batch=700) as dev:
+            sms = dev.query(4)
+            out[flag] = dev.log_posterior(a.theta, n_div=1.0)
+            if flag is None:
+                for W in (1, 2 * sms, 2 * sms + 1, 3 * sms + 5):      # both sides of the per-launch choice
+                    assert np.array_equal(dev.log_posterior(a.theta[:W], n_div=1.0), out[None][:W], equal_nan=True), W
+                struct = dev.log_posterior(a.theta, n_div=1.0, mode="structured")
+    assert np.array_equal(out[None], out["0"], equal_nan=True) and np.array_equal(out[None], out["1"], equal_nan=True)
+    idx = np.flatnonzero(np.isfinite(out[None]))[:32]
+    _cmp_logp(out[None][idx], cf.log_posterior(img.to_flat(), a.theta[idx], n_div=1.0))
+    fin = np.isfinite(out[None])
+    assert rel_err(struct[fin], out[None][fin]) < TOL_LOGP
 
 
 @pytest.mark.parametrize("name", ["TOY", "C1", "C3B"])
