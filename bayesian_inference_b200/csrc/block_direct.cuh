@@ -56,8 +56,10 @@ __host__ __device__ inline size_t block_direct_smem_bytes(int FB) {
 
 // grid (n_blocks, ceil(W / (BD_WARPS * wpw))): warp u of CTA (b, y) takes walkers y * BD_WARPS * wpw + u + BD_WARPS * i, i < wpw.
 // FB = f padded to a multiple of 8 (template: the matrix row lives in FB registers).
+// Resident CTAs per SM by row length: the kernel is bound by the latency of its dependent shuffle / FMA chains (ncu: FP64
+// pipe 32 %, issue slots 44 % busy at 16 warps per SM), so the shorter rows trade registers for warps.
 template <int FB>
-__global__ void __launch_bounds__(BD_THREADS, 2) block_direct_kernel(const BdBlock* __restrict__ blocks, int nB, long long W, int wpw,
+__global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2)) block_direct_kernel(const BdBlock* __restrict__ blocks, int nB, long long W, int wpw,
                                                                      int Ptot, int K0, const double* __restrict__ m,
                                                                      const double* __restrict__ v, const double* __restrict__ Trow,
                                                                      const double* __restrict__ e, const double* __restrict__ Aall,
