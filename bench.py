@@ -72,6 +72,16 @@ def gp_flops_per_eval(groups) -> float:
     return float(sum(g.n_pc * (g.n_design ** 2 + 4 * g.n_design) for g in groups))
 
 
+K1_FP64_INSTR_PER_VALUE = 33   # distance 2d, sqrt 9, exp 12 (csrc/gp_predict.cuh): each one issue slot of the FP64 datapath
+
+
+def gp_datapath_frac(groups, W: int, ms: float) -> float:
+    """Share of the one FP64 datapath (DMMA and DFMA/DADD/DMUL issue on the same pipe) the K1+K2 launch keeps busy:
+    K2's flops as FMA equivalents + K1's FP64 instructions (one FMA slot each), over the peak FMA rate."""
+    fma = sum(g.n_pc * ((g.n_design ** 2 + 4 * g.n_design) / 2.0 + K1_FP64_INSTR_PER_VALUE * g.n_design) for g in groups)
+    return fma * W / (ms * 1e-3) / (FP64_TENSOR_PEAK_TFLOPS * 1e12 / 2.0)
+
+
 # ---- clocks ---------------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
     def __init__(self, index: int, period: float = 0.05):
@@ -456,7 +466,8 @@ def main() -> None:
                     stages={"gp_predict_ms": gp[0] / max(gp[1], 1), "chol_loglik_ms": ch[0] / max(ch[1], 1),
                             "gp_tflops": gp_flops_per_eval(img.groups) * W / (gp[0] / max(gp[1], 1) * 1e-3) / 1e12 if gp[1] else None,
                             "gp_frac_of_fp64_peak": gp_flops_per_eval(img.groups) * W / (gp[0] / max(gp[1], 1) * 1e-3) / 1e12
-                            / FP64_TENSOR_PEAK_TFLOPS if gp[1] else None},
+                            / FP64_TENSOR_PEAK_TFLOPS if gp[1] else None,
+                            "gp_fp64_datapath_frac": gp_datapath_frac(img.groups, W, gp[0] / max(gp[1], 1)) if gp[1] else None},
                     clocks=clocks)
 
     # ---- extra legs (N = 1): sustained load, and the literally dense C3b layout --------------------------------------

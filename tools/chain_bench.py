@@ -57,20 +57,23 @@ def main():
                      experimental_results=an.experimental_results, sigma_exp=an.sigma_exp)
     W, d = spec.n_walkers, spec.d
     x0 = np.random.RandomState(1).uniform(0.3, 0.7, (W, d))
+    modes = a.mode.split(",")
     out = {"workload": spec.name, "walkers": W, "steps": a.steps, "mode": a.mode, "n_obs": img.n_features, "n_gpus": world,
            "block": a.block, "scaling": "strong (one ensemble, proposals of a half-step split over the ranks)" if world > 1 else "single GPU"}
     names = a.samplers.split(",") if a.samplers else (["device", "device_graph"] if world > 1 else
                                                       ["host", "device", "device_graph", "device_philox", "device_philox_graph"])
-    with DeviceEmulator(img, device=local_rank, max_batch=max(W, a.closures * W)) as dev:
-        def host_fn(X):
-            return dev.log_posterior(X, n_div=1.0, mode=a.mode)
+    dev = DeviceEmulator(img, device=local_rank, max_batch=max(W, a.closures * W))
+    sums = {}
+    for mode in modes:
+        def host_fn(X, mode=mode):
+            return dev.log_posterior(X, n_div=1.0, mode=mode)
 
         mk = {"host": lambda: StretchEnsemble(W, d, ShardedLogProb(host_fn) if world > 1 else host_fn, seed=3),
-              "device": lambda: DeviceStretchEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block),
-              "device_graph": lambda: DeviceStretchEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block, graph=True),
-              "device_philox": lambda: DevicePhiloxEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block),
-              "device_philox_graph": lambda: DevicePhiloxEnsemble(W, d, dev, mode=a.mode, seed=3, block=a.block, graph=True)}
-        sums = {}
+              "device": lambda: DeviceStretchEnsemble(W, d, dev, mode=mode, seed=3, block=a.block),
+              "device_graph": lambda: DeviceStretchEnsemble(W, d, dev, mode=mode, seed=3, block=a.block, graph=True),
+              "device_philox": lambda: DevicePhiloxEnsemble(W, d, dev, mode=mode, seed=3, block=a.block),
+              "device_philox_graph": lambda: DevicePhiloxEnsemble(W, d, dev, mode=mode, seed=3, block=a.block, graph=True)}
+        pre = "" if len(modes) == 1 else mode + "_"
         for name in names:
             s = mk[name]()
             s.run_mcmc(x0, max(10, a.block) if "graph" in name else 10)      # warm-up (captures the block graph)
@@ -93,61 +96,66 @@ def main():
                 t = torch.tensor([dt], dtype=torch.float64, device="cuda")
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 dt = float(t.item())
-            out[name] = {"seconds": dt, "steps_per_s": a.steps / dt, "evals_per_s": (a.steps + 1) * W / dt,
-                         "half_step_us": dt / (2 * a.steps) * 1e6, "acceptance": float(s.acceptance_fraction.mean()),
-                         "graph_replays": getattr(s, "n_graph_replays", 0)}
-            sums[name] = float(np.sum(s.get_chain()))
-        if world > 1:
-            # the collective alone: the very call of a half-step (W/2 log-probabilities, ceil(W/2/N) per rank), CUDA events
-            per = (W // 2 + world - 1) // world
-            send = torch.zeros(per, dtype=torch.float64, device="cuda")
-            recv = torch.empty(per * world, dtype=torch.float64, device="cuda")
-            for _ in range(20):
-                dist.all_gather_into_tensor(recv, send)
-            torch.cuda.synchronize()
-            dist.barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            n_ag = 500
-            e0.record()
-            for _ in range(n_ag):
-                dist.all_gather_into_tensor(recv, send)
-            e1.record()
-            torch.cuda.synchronize()
-            ag_us = e0.elapsed_time(e1) / n_ag * 1e3
-            t = torch.tensor([ag_us], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ag_us = float(t.item())
-            best = min((out[n]["half_step_us"] for n in names))
-            out["all_gather"] = {"bytes_per_rank": per * 8, "us_per_call_back_to_back": ag_us, "share_of_best_half_step": ag_us / best}
-        if a.closures and world == 1:
-            from bayesian_inference_b200.ensemble import BatchedClosureEnsemble
+            out[pre + name] = {"seconds": dt, "steps_per_s": a.steps / dt, "evals_per_s": (a.steps + 1) * W / dt,
+                               "half_step_us": dt / (2 * a.steps) * 1e6, "acceptance": float(s.acceptance_fraction.mean()),
+                               "graph_replays": getattr(s, "n_graph_replays", 0)}
+            sums[pre + name] = float(np.sum(s.get_chain()))
+            s._buf = None                  # drop the captured graph (it holds NCCL kernels) before the communicator goes
+            del s
+        emcee_stream = [pre + n for n in names if "philox" not in n]
+        out[pre + "identical_chain_emcee_stream"] = len({sums[n] for n in emcee_stream}) <= 1
+        philox = [pre + n for n in names if "philox" in n]
+        if philox:
+            out[pre + "identical_chain_philox"] = len({sums[n] for n in philox}) <= 1
+    if world > 1:
+        # the collective alone: the very call of a half-step (W/2 log-probabilities, ceil(W/2/N) per rank), CUDA events
+        per = (W // 2 + world - 1) // world
+        send = torch.zeros(per, dtype=torch.float64, device="cuda")
+        recv = torch.empty(per * world, dtype=torch.float64, device="cuda")
+        for _ in range(20):
+            dist.all_gather_into_tensor(recv, send)
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n_ag = 500
+        e0.record()
+        for _ in range(n_ag):
+            dist.all_gather_into_tensor(recv, send)
+        e1.record()
+        torch.cuda.synchronize()
+        ag_us = e0.elapsed_time(e1) / n_ag * 1e3
+        t = torch.tensor([ag_us], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ag_us = float(t.item())
+        best = min(v["half_step_us"] for v in out.values() if isinstance(v, dict) and "half_step_us" in v)
+        out["all_gather"] = {"bytes_per_rank": per * 8, "us_per_call_back_to_back": ag_us, "share_of_best_half_step": ag_us / best}
+    if a.closures and world == 1:
+        from bayesian_inference_b200.ensemble import BatchedClosureEnsemble
 
-            C_ = a.closures
-            rng = np.random.default_rng(9)
-            y, ye = an.experimental_results["y"], an.experimental_results["y_err"]
-            dev.set_data_sets(np.stack([y * (1.0 + 0.03 * rng.normal(size=y.shape)) for _ in range(C_)]), np.stack([ye] * C_))
-            starts = np.stack([np.random.RandomState(100 + c).uniform(0.3, 0.7, (W, d)) for c in range(C_)])
-            BatchedClosureEnsemble(W, d, dev, [np.random.RandomState(c) for c in range(C_)], mode=a.mode, block=a.block).run_mcmc(starts, 5)
-            ens = BatchedClosureEnsemble(W, d, dev, [np.random.RandomState(c) for c in range(C_)], mode=a.mode, block=a.block)
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            ens.run_mcmc(starts, a.steps)
-            torch.cuda.synchronize()
-            dt = time.perf_counter() - t0
-            out["closures_batched"] = {"chains": C_, "seconds": dt, "chain_steps_per_s": C_ * a.steps / dt,
-                                       "evals_per_s": ens.n_log_prob_rows / dt,
-                                       "speedup_vs_serial_device_chains": (C_ * a.steps / dt) / out["device"]["steps_per_s"]
-                                       if "device" in out else None}
-    emcee_stream = [n for n in names if "philox" not in n]
-    out["identical_chain_emcee_stream"] = len({sums[n] for n in emcee_stream}) <= 1
-    philox = [n for n in names if "philox" in n]
-    if philox:
-        out["identical_chain_philox"] = len({sums[n] for n in philox}) <= 1
+        C_, mode = a.closures, modes[0]
+        rng = np.random.default_rng(9)
+        y, ye = an.experimental_results["y"], an.experimental_results["y_err"]
+        dev.set_data_sets(np.stack([y * (1.0 + 0.03 * rng.normal(size=y.shape)) for _ in range(C_)]), np.stack([ye] * C_))
+        starts = np.stack([np.random.RandomState(100 + c).uniform(0.3, 0.7, (W, d)) for c in range(C_)])
+        BatchedClosureEnsemble(W, d, dev, [np.random.RandomState(c) for c in range(C_)], mode=mode, block=a.block).run_mcmc(starts, 5)
+        ens = BatchedClosureEnsemble(W, d, dev, [np.random.RandomState(c) for c in range(C_)], mode=mode, block=a.block)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ens.run_mcmc(starts, a.steps)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        out["closures_batched"] = {"chains": C_, "mode": mode, "seconds": dt, "chain_steps_per_s": C_ * a.steps / dt,
+                                   "evals_per_s": ens.n_log_prob_rows / dt}
     if rank == 0:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
+    torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+    sys.stdout.flush()
+    # no destroy_process_group: tearing the communicator down after NCCL kernels were captured into CUDA graphs hung the
+    # 2-GPU run of this tool at exit (300 s timeout); every rank has passed the barrier, so leave without the teardown
+    os._exit(0)
 
 
 if __name__ == "__main__":
