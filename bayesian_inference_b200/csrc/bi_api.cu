@@ -100,7 +100,7 @@ struct bi_handle_s {
     int *dInfoW = nullptr, *dWbK = nullptr;
     // block-direct evaluation of BI_MODE_STRUCTURED (every observable block fits one warp: f_b <= 31)
     int bd_state = 0;             // 0 not looked at yet, 1 usable, -1 not applicable (falls back to the tile-skipping kernel)
-    int bdFB = 0;
+    int bdFB = 0, bdNks = 0;      // row length padded to a multiple of 8; k-steps of 4 principal components (max over blocks)
     std::vector<BdBlock> bdBlocks;
     BdBlock* dBdBlocks = nullptr;
     double* dBdA[2] = {nullptr, nullptr};      // [0] n_div = 1 (never rewritten), [1] the last other divisor
@@ -1139,6 +1139,20 @@ static int ensure_block_direct(bi_handle h) {
     }
     h->bdFB = (fmax + 7) / 8 * 8;
     h->bd_a_tot = a_tot;
+    int pmax = 0;
+    for (const BdBlock& B : h->bdBlocks) pmax = std::max(pmax, B.P);
+    h->bdNks = (pmax + 3) / 4;
+    if (block_direct_smem_bytes(h->bdFB, h->bdNks) > 113 * 1024) return 0;   // two CTAs per SM must fit (108.7 KB at FB = 32, P = 64)
+    {
+        cudaError_t e_ = cudaSuccess;
+        switch (h->bdFB) {
+            case 8: e_ = allow_max_smem(block_direct_kernel<8>); break;
+            case 16: e_ = allow_max_smem(block_direct_kernel<16>); break;
+            case 24: e_ = allow_max_smem(block_direct_kernel<24>); break;
+            default: e_ = allow_max_smem(block_direct_kernel<32>); break;
+        }
+        if (e_ != cudaSuccess) { h->err = std::string("block_direct smem: ") + cudaGetErrorString(e_); return (int)e_; }
+    }
     int rc = upload(h, &h->dBdBlocks, h->bdBlocks.data(), h->bdBlocks.size());
     if (rc) return rc;
     for (int i = 0; i < 2; ++i)
@@ -1174,7 +1188,7 @@ static int run_block_direct(bi_handle h, const double* dTheta, long long W, doub
         CK(cudaGetLastError());
         h->bd_ndiv[slot] = n_div;
     }
-    const size_t smem = block_direct_smem_bytes(h->bdFB);
+    const size_t smem = block_direct_smem_bytes(h->bdFB, h->bdNks);
     for (long long w0 = 0; w0 < W; w0 += h->max_batch) {
         const long long wb = std::min<long long>(h->max_batch, W - w0);
         int rc = launch_gp(h, dTheta + w0 * h->d, wb, h->dM, h->dV, s);
@@ -1186,7 +1200,7 @@ static int run_block_direct(bi_handle h, const double* dTheta, long long W, doub
         {
             ProfScope ps(h, 1, s);
 #define BD_LAUNCH(FBV)                                                                                                       \
-    block_direct_kernel<FBV><<<grid, BD_THREADS, smem, s>>>(h->dBdBlocks, nB, wb, wpw, h->Ptot, h->K0, h->dM, h->dV, h->dTrow, dEall, \
+    block_direct_kernel<FBV><<<grid, BD_THREADS, smem, s>>>(h->dBdBlocks, nB, wb, wpw, h->Ptot, h->K0, h->bdNks, h->dM, h->dV, h->dTrow, dEall, \
                                                             dAall, h->dBdPart, h->dBdBad, dSetId ? dSetId + w0 : nullptr, e_stride,  \
                                                             a_stride)
             switch (h->bdFB) {

@@ -49,35 +49,55 @@ __global__ void __launch_bounds__(256) block_a_kernel(const BdBlock* __restrict_
     }
 }
 
-__host__ __device__ inline size_t block_direct_smem_bytes(int FB) {
-    // sTt (BD_PMAX x FB) + sA (32 x FB: rows f..30 identity, row 31 = e_b) + per warp v and m (2 x BD_PMAX)
-    return sizeof(double) * ((size_t)BD_PMAX * FB + (size_t)32 * FB + (size_t)BD_WARPS * 2 * BD_PMAX);
+__host__ __device__ inline size_t block_direct_smem_bytes(int FB, int nks) {
+    // CTA: sTf (T_b as DMMA operand fragments, FB/8 x nks x 32) + sA (32 x FB: A_b rows, identity rows f.., row 31 = e_b)
+    // per warp: sC ((FB+1) x (FB+2): the assembled block, row-major) + sCol (2 x 32: column broadcast) + v and m (2 x 4 nks)
+    return sizeof(double) * ((size_t)(FB / 8) * nks * 32 + (size_t)32 * FB +
+                             (size_t)BD_WARPS * ((size_t)(FB + 1) * (FB + 2) + 64 + 8 * nks));
 }
 
 // grid (n_blocks, ceil(W / (BD_WARPS * wpw))): warp u of CTA (b, y) takes walkers y * BD_WARPS * wpw + u + BD_WARPS * i, i < wpw.
-// FB = f padded to a multiple of 8 (template: the matrix row lives in FB registers).
-// Resident CTAs per SM by row length: the kernel is bound by the latency of its dependent shuffle / FMA chains (ncu: FP64
-// pipe 32 %, issue slots 44 % busy at 16 warps per SM), so the shorter rows trade registers for warps.
+// FB = f padded to a multiple of 8 (template: the matrix row lives in FB registers); nksmax = ceil(max P / 4).
+//
+// Per (walker, block), one warp:
+//  1. assembly on the FP64 tensor pipe: [T_b diag(v) ; m^T] T_b^T by mma.sync m8n8k4 -- lower 8 x 8 tiles of the f x f block plus
+//     one row of tiles for the augmented row (T_b m); T_b sits in shared memory as operand fragments, staged once per CTA
+//     (a CTA works on one block for a batch of walkers), and the same fragment is the B operand and, scaled by v, the A
+//     operand: 5 shared-memory loads per 9 DMMAs;
+//  2. accumulator fragments -> the warp's row-major tile in shared memory -> one matrix row per lane (+ A_b, theta
+//     independent; lane 31 = the augmented row dy_b = e_b + T_b m);
+//  3. right-looking Cholesky in registers; column c of the current matrix is broadcast through shared memory (one store,
+//     one 16-byte broadcast load per two multipliers) -- the first version used two SHFL per multiplier and was bound by the
+//     SM's shuffle / load-store unit (ncu: 1073 of 3200 instructions per task, short-scoreboard + MIO-throttle stalls 50 %).
+//     The update uses u = a[r][c] / pivot and the unscaled column, L[r][c] L[c2][c] = u * a[c2][c].
+// Resident CTAs per SM by row length (registers for warps).
 template <int FB>
-__global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2)) block_direct_kernel(const BdBlock* __restrict__ blocks, int nB, long long W, int wpw,
-                                                                     int Ptot, int K0, const double* __restrict__ m,
-                                                                     const double* __restrict__ v, const double* __restrict__ Trow,
-                                                                     const double* __restrict__ e, const double* __restrict__ Aall,
-                                                                     double* __restrict__ part, int* __restrict__ bad_out,
-                                                                     const int* __restrict__ set_id, long long e_stride,
-                                                                     long long a_stride) {
+__global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2)) block_direct_kernel(
+    const BdBlock* __restrict__ blocks, int nB, long long W, int wpw, int Ptot, int K0, int nksmax, const double* __restrict__ m,
+    const double* __restrict__ v, const double* __restrict__ Trow, const double* __restrict__ e, const double* __restrict__ Aall,
+    double* __restrict__ part, int* __restrict__ bad_out, const int* __restrict__ set_id, long long e_stride, long long a_stride) {
+    constexpr int NFR = FB / 8;                               // 8-row fragments holding matrix rows
+    constexpr bool AUGF = FB < 32;                            // the augmented row has a fragment row of its own
+    constexpr int LDC = FB + 2;
+    constexpr int NCOL = (FB == 32) ? 31 : FB;                // columns eliminated (column 31 would be the augmented row's own)
+    constexpr int AUGROW = (FB == 32) ? 31 : FB;              // row of sC holding the augmented row
     extern __shared__ __align__(16) unsigned char bd_smem[];
-    double* sTt = reinterpret_cast<double*>(bd_smem);        // [p][c]  T_b transposed, columns c >= f are zero
-    double* sA = sTt + BD_PMAX * FB;                          // [r][c]  A_b, identity rows f..30, row 31 = e_b
-    double* sVM = sA + 32 * FB;                               // [warp][2][BD_PMAX]
+    double* sTf = reinterpret_cast<double*>(bd_smem);        // [mf][ks][lane] = T_b[8 mf + g][4 ks + t]
+    double* sA = sTf + (size_t)NFR * nksmax * 32;             // [r][c]  A_b, identity rows f..30, row 31 = e_b
+    double* sW = sA + 32 * FB;                                // per-warp scratch
     const BdBlock B = blocks[blockIdx.x];
     const int f = B.f, P = B.P;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int NCOL = (FB == 32) ? 31 : FB;                // columns eliminated (column 31 would be the augmented row's own)
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const int wstride = (FB + 1) * LDC + 64 + 8 * nksmax;
+    double* sC = sW + (size_t)warp * wstride;                 // [(FB + 1)][LDC]
+    double* sCol = sC + (FB + 1) * LDC;                       // [2][32]
+    double* sV = sCol + 64;                                   // [4 nksmax]
+    double* sM = sV + 4 * nksmax;
 
-    for (int idx = tid; idx < BD_PMAX * FB; idx += BD_THREADS) {
-        const int p = idx / FB, c = idx - p * FB;
-        sTt[idx] = (p < P && c < f) ? __ldg(Trow + (size_t)(B.row0 + c) * K0 + B.col0 + p) : 0.0;
+    for (int idx = tid; idx < NFR * nksmax * 32; idx += BD_THREADS) {
+        const int l = idx & 31, ks = (idx >> 5) % nksmax, mf = (idx >> 5) / nksmax;
+        const int r = 8 * mf + (l >> 2), p = 4 * ks + (l & 3);
+        sTf[idx] = (r < f && p < P) ? __ldg(Trow + (size_t)(B.row0 + r) * K0 + B.col0 + p) : 0.0;
     }
     for (int idx = tid; idx < 32 * FB; idx += BD_THREADS) {
         const int r = idx / FB, c = idx - r * FB;
@@ -87,76 +107,119 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
         else x = (r == c) ? 1.0 : 0.0;
         sA[idx] = x;
     }
+    for (int idx = lane; idx < (FB + 1) * LDC; idx += 32) sC[idx] = 0.0;   // tiles above the diagonal are never written
     __syncthreads();
 
-    double* sV = sVM + warp * 2 * BD_PMAX;
-    double* sM = sV + BD_PMAX;
+    const bool is_aug = lane == 31;
+    const bool has_row = lane < FB || is_aug;
+    const int nks = (P + 3) >> 2;
     const long long w_base = (long long)blockIdx.y * BD_WARPS * wpw + warp;
     for (int it = 0; it < wpw; ++it) {
         const long long w = w_base + (long long)it * BD_WARPS;
         if (w >= W) break;                                    // warp-uniform
         __syncwarp();
-        for (int p = lane; p < BD_PMAX; p += 32) {
+        for (int p = lane; p < 4 * nks; p += 32) {
             const bool ok = p < P;
             sV[p] = ok ? __ldg(v + w * Ptot + B.col0 + p) : 0.0;
             sM[p] = ok ? __ldg(m + w * Ptot + B.col0 + p) : 0.0;
         }
         __syncwarp();
-        // ---- assembly: row `lane` of [C_b ; dy_b]
+        // ---- 1. assembly on the tensor pipe
+        {
+            double acc[NFR][NFR][2], aug[NFR][2];
+#pragma unroll
+            for (int mi = 0; mi < NFR; ++mi) {
+                aug[mi][0] = aug[mi][1] = 0.0;
+#pragma unroll
+                for (int nf = 0; nf < NFR; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
+            }
+            for (int ks = 0; ks < nks; ++ks) {
+                double tf[NFR], ta[NFR];
+                const double vk = sV[4 * ks + t], mk = sM[4 * ks + t];
+#pragma unroll
+                for (int mf = 0; mf < NFR; ++mf) {
+                    tf[mf] = sTf[((size_t)mf * nksmax + ks) * 32 + lane];
+                    ta[mf] = tf[mf] * vk;
+                }
+                if (!AUGF && g == 7) ta[NFR - 1] = mk;        // FB = 32: row 31 of the last fragment is the augmented row
+#pragma unroll
+                for (int mi = 0; mi < NFR; ++mi)
+#pragma unroll
+                    for (int nf = 0; nf <= mi; ++nf) dmma(acc[mi][nf], ta[mi], tf[nf]);
+                if (AUGF) {
+                    const double aa = (g == 7) ? mk : 0.0;
+#pragma unroll
+                    for (int nf = 0; nf < NFR; ++nf) dmma(aug[nf], aa, tf[nf]);
+                }
+            }
+            // ---- 2. fragments -> row-major tile of this warp
+#pragma unroll
+            for (int mi = 0; mi < NFR; ++mi)
+#pragma unroll
+                for (int nf = 0; nf <= mi; ++nf)
+                    *reinterpret_cast<double2*>(sC + (8 * mi + g) * LDC + 8 * nf + 2 * t) = make_double2(acc[mi][nf][0], acc[mi][nf][1]);
+            if (AUGF && g == 7) {
+#pragma unroll
+                for (int nf = 0; nf < NFR; ++nf)
+                    *reinterpret_cast<double2*>(sC + AUGROW * LDC + 8 * nf + 2 * t) = make_double2(aug[nf][0], aug[nf][1]);
+            }
+        }
+        __syncwarp();
         double a[FB];
-        const bool is_aug = lane == 31;
-        if (set_id == nullptr) {
-            const double2* init = reinterpret_cast<const double2*>(sA + lane * FB);
+        {
+            const double2* crow = reinterpret_cast<const double2*>(sC + (is_aug ? AUGROW : (lane < FB ? lane : 0)) * LDC);
+            if (set_id == nullptr) {
+                const double2* init = reinterpret_cast<const double2*>(sA + lane * FB);
 #pragma unroll
-            for (int c = 0; c < FB; c += 2) {
-                const double2 x = init[c >> 1];
-                a[c] = x.x;
-                a[c + 1] = x.y;
-            }
-        } else {
-            // several experimental data sets on one image (closure tests, steer_analysis.py:168-183): A_b and e_b of this
-            // walker's set come straight from global memory (L2 resident), everything after that is the same arithmetic
-            const long long sid = set_id[w];
-            const double* As = Aall + sid * a_stride + B.a_off + (size_t)(lane < f ? lane : 0) * f;
-            const double* es = e + sid * e_stride + B.row0;
+                for (int c = 0; c < FB; c += 2) {
+                    const double2 x = init[c >> 1], y = crow[c >> 1];
+                    a[c] = has_row ? x.x + y.x : 0.0;
+                    a[c + 1] = has_row ? x.y + y.y : 0.0;
+                }
+            } else {
+                // several experimental data sets on one image (closure tests, steer_analysis.py:168-183): A_b and e_b of this
+                // walker's set come straight from global memory (L2 resident), everything else is the same arithmetic
+                const long long sid = set_id[w];
+                const double* As = Aall + sid * a_stride + B.a_off + (size_t)(lane < f ? lane : 0) * f;
+                const double* es = e + sid * e_stride + B.row0;
 #pragma unroll
-            for (int c = 0; c < FB; ++c) {
-                double x = (lane == c) ? 1.0 : 0.0;
-                if (c < f) {
-                    if (is_aug) x = __ldg(es + c);
-                    else if (lane < f) x = __ldg(As + c);
-                } else if (is_aug) x = 0.0;
-                a[c] = x;
-            }
-        }
-        const int trow = (lane < f) ? lane : 0;               // lanes f..30 (identity rows) use coefficient 0
-        for (int p = 0; p < P; ++p) {
-            double coef = sTt[p * FB + trow] * sV[p];
-            if (lane >= f) coef = 0.0;
-            if (is_aug) coef = sM[p];
-            const double2* tp = reinterpret_cast<const double2*>(sTt + p * FB);
-#pragma unroll
-            for (int c = 0; c < FB; c += 2) {
-                const double2 t2 = tp[c >> 1];
-                a[c] = fma(coef, t2.x, a[c]);
-                a[c + 1] = fma(coef, t2.y, a[c + 1]);
+                for (int c = 0; c < FB; c += 2) {
+                    const double2 y = crow[c >> 1];
+                    double x0 = (lane == c) ? 1.0 : 0.0, x1 = (lane == c + 1) ? 1.0 : 0.0;
+                    if (c < f) {
+                        if (is_aug) x0 = __ldg(es + c);
+                        else if (lane < f) x0 = __ldg(As + c);
+                    } else if (is_aug) x0 = 0.0;
+                    if (c + 1 < f) {
+                        if (is_aug) x1 = __ldg(es + c + 1);
+                        else if (lane < f) x1 = __ldg(As + c + 1);
+                    } else if (is_aug) x1 = 0.0;
+                    a[c] = has_row ? x0 + y.x : 0.0;
+                    a[c + 1] = has_row ? x1 + y.y : 0.0;
+                }
             }
         }
-        // ---- right-looking Cholesky in registers; lane 31 becomes z = L^-1 dy
+        // ---- 3. right-looking Cholesky in registers; lane 31 becomes z = L^-1 dy
         int bad = 0;
         double mypiv = 1.0, quad = 0.0;
 #pragma unroll
         for (int c = 0; c < NCOL; ++c) {
-            const double piv = shfl_d(a[c], c);
+            double* cb = sCol + (c & 1) * 32;
+            cb[lane] = a[c];                                  // column c of the current matrix, all rows
+            __syncwarp();
+            const double piv = cb[c];
             if (!(piv > 0.0) && bad == 0) bad = c + 1;
             if (lane == c) mypiv = piv;
             const double rinv = rsqrt(piv);
-            a[c] *= rinv;
+            const double u = a[c] * (rinv * rinv);            // a[r][c] / pivot
+            a[c] *= rinv;                                     // L[r][c]; on lane 31: z_c
             if (is_aug) quad = fma(a[c], a[c], quad);
 #pragma unroll
-            for (int c2 = c + 1; c2 < NCOL; ++c2) {
-                const double l = shfl_d(a[c], c2);
-                a[c2] = fma(-a[c], l, a[c2]);
+            for (int e2 = 0; e2 < FB; e2 += 2) {             // columns in aligned pairs: one 16-byte broadcast load per two
+                if (e2 + 1 <= c || e2 >= NCOL) continue;      // (all of this resolves at compile time: c, e2 are unrolled)
+                const double2 l2 = *reinterpret_cast<const double2*>(cb + e2);
+                if (e2 > c) a[e2] = fma(-u, l2.x, a[e2]);
+                if (e2 + 1 < NCOL) a[e2 + 1] = fma(-u, l2.y, a[e2 + 1]);
             }
         }
         const double ld = warp_sum((lane < f) ? 0.5 * log(mypiv) : 0.0);

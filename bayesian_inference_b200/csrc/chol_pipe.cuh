@@ -39,7 +39,10 @@ constexpr int PIPE_CONSUMERS_WIDE = 16;
 // 4 consumers, three CTAs per SM: for few-tile problems (F <= ~320), where a panel has at most a dozen strips and the
 // walker's time is the chain potrf -> solve -> next diagonal tile, a third walker in flight per SM is worth more than wider
 // rounds (measured on the C1 shape, profiles/r02_notes.md).
-constexpr int PIPE_CONSUMERS_SMALL = 4;
+#ifndef PIPE_NC_SMALL
+#define PIPE_NC_SMALL 4   // experiment knob: 5 consumers x 3 CTAs needs -DPIPE_NSTAGES=3 to fit the shared memory
+#endif
+constexpr int PIPE_CONSUMERS_SMALL = PIPE_NC_SMALL;
 __host__ __device__ constexpr int pipe_threads(int nc) { return (nc + 2) * 32; }   // + producer + factor warp
 #ifndef PIPE_NSTAGES
 #define PIPE_NSTAGES 4   // measured: 3, 4, 6 and 8 stages all leave the consumers' wait at 25-30 % -- the ring is not latency bound
