@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--reps", type=int, default=6)
     ap.add_argument("--save", default=None)
     ap.add_argument("--check", default=None)
+    ap.add_argument("--walkers", type=int, default=0)
     a = ap.parse_args()
     import torch
 
@@ -34,7 +35,7 @@ def main():
     dev = DeviceEmulator(img, max_batch=8192)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     rng = np.random.default_rng(1)
-    W = max(64, min(2048, int((4 << 30) / (8 * F * F))))
+    W = a.walkers or max(64, min(2048, int((4 << 30) / (8 * F * F))))
     th = torch.from_numpy(np.ascontiguousarray(rng.uniform(0.05, 0.95, size=(W, d)))).cuda()
     mean = torch.empty((W, F), dtype=torch.float64, device="cuda")
     cov = torch.empty((W, F, F), dtype=torch.float64, device="cuda")
