@@ -6,14 +6,15 @@
 //     logp = sum_b [ -1/2 dy_b^T C_b^-1 dy_b - sum log diag chol(C_b) ],   C_b = A_b + T_b D T_b^T,  dy_b = e_b + T_b m
 // (structured variant: "if f_b <= P: direct f_b x f_b Cholesky").  With f_b <= 31 a block lives in ONE
 // warp's registers, one matrix row per lane:
-//   * assembly  a[r][c] = A_b[r][c] + sum_p (T[r][p] v_p) T[c][p]  -- p outer, c inner; T_b is staged transposed in shared
-//     memory once per CTA (a CTA works on one block for a batch of walkers), so T[c][p], T[c+1][p] come as one broadcast
-//     16-byte load per two FMAs;
-//   * lane 31 carries the augmented row dy_b (the same instruction stream with m in place of T[r][.] v and e_b in place of
-//     A_b[r][.]), so the right-looking elimination turns it into z = L^-1 dy and the quadratic form is sum z^2: no separate
-//     substitution (the device K4 kernels use the same augmentation);
-//   * right-looking Cholesky in registers: pivot and multipliers by warp shuffles, rows between f and the padded size are
-//     identity rows.
+//   * assembly  a[r][c] = A_b[r][c] + sum_p (T[r][p] v_p) T[c][p] on the FP64 tensor pipe (mma.sync m8n8k4): T_b is staged
+//     in shared memory once per CTA as operand fragments (a CTA works on one block for a batch of walkers); only the
+//     lower 8 x 8 tiles are computed; the accumulators go through a per-warp row-major tile to one row per lane;
+//   * lane 31 carries the augmented row dy_b (one more fragment row in the assembly: m in place of T[r][.] v, e_b in place
+//     of A_b[r][.]), so the right-looking elimination turns it into z = L^-1 dy and the quadratic form is sum z^2: no
+//     separate substitution (the device K4 kernels use the same augmentation);
+//   * right-looking Cholesky in registers: the pivot column is broadcast through a double-buffered 32-entry line of shared
+//     memory (the first version used warp shuffles and was bound by the shuffle / load-store unit); rows between f and the
+//     padded size are identity rows.
 // The per-block terms go to a (W, n_blocks) scratch and block_combine_kernel adds them in block order (deterministic) and
 // applies the strict prior box (log_posterior.py:63-64).
 //
