@@ -27,6 +27,7 @@ EXPORTS = [
     "bi_stretch_propose", "bi_stretch_accept", "bi_set_data_sets", "bi_log_posterior_sets", "bi_stretch_randoms_philox",
     "bi_trainer_create", "bi_trainer_lml", "bi_trainer_lml_host", "bi_trainer_factor", "bi_trainer_factor_host",
     "bi_trainer_destroy", "bi_trainer_last_error", "bi_trainer_launches",
+    "bi_loglikelihood_noalloc",
 ]
 
 # entry points that return an int status (0 ok, <0 bad argument, >0 CUDA error code); named one by one so that adding
@@ -37,6 +38,7 @@ INT_STATUS_EXPORTS = [
     "bi_log_posterior", "bi_log_posterior_host", "bi_loglikelihood_host",
     "bi_stretch_propose", "bi_stretch_accept", "bi_set_data_sets", "bi_log_posterior_sets", "bi_stretch_randoms_philox",
     "bi_trainer_create", "bi_trainer_lml", "bi_trainer_lml_host", "bi_trainer_factor", "bi_trainer_factor_host",
+    "bi_loglikelihood_noalloc",
 ]
 
 MODE = {"dense": 0, "structured": 1, "woodbury": 2}

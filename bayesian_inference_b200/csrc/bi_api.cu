@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <utility>
 #include <vector>
@@ -1687,3 +1688,84 @@ int bi_trainer_factor_host(bi_trainer t, const double* theta, const int32_t* y_i
 }
 
 }  // extern "C"
+
+// ---- bi_loglikelihood_noalloc: the explicit (dy, C) log-likelihood for callers that may not allocate ----------------------
+// No counterpart in the reference; added at the request of the run's operators (callers under CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  Same kernel as bi_loglikelihood_host (chol_loglik_kernel<true>), but
+// its per-CTA scratch (the factor's strictly-lower tiles + one z tile per panel) and the kmin / imax table live in ONE
+// file-scope device array of fixed size instead of cudaMalloc'd buffers.  Every GPU that loads the library holds
+// BI_NOALLOC_SCRATCH_BYTES (8 MiB + 256 B) until the process exits.  All calls share the array: the kernel writes every
+// scratch tile before it reads it and the table is rewritten by every call, so nothing has to start at zero, but two
+// calls that overlap on the GPU (different streams, no ordering) race on it.
+// BI_NOALLOC_MAX_F (256: 8 x 8 tiles of 32 x 32) comes from include/bi_b200.h
+#define BI_NOALLOC_WS_DOUBLES (1 << 20)           /* 8 MiB of factor scratch */
+#define BI_NOALLOC_TABLE_DOUBLES 32               /* 256 B: kmin[8], imax[8] as int32 */
+#define BI_NOALLOC_SCRATCH_BYTES (8 * (BI_NOALLOC_WS_DOUBLES + BI_NOALLOC_TABLE_DOUBLES))
+static __device__ __align__(256) double g_noalloc_scratch[BI_NOALLOC_TABLE_DOUBLES + BI_NOALLOC_WS_DOUBLES];
+
+namespace {
+// device code may name the array directly: dense table (kmin = 0, imax = nt - 1) for this call's tile count
+__global__ void noalloc_table_kernel(int nt) {
+    int* tab = reinterpret_cast<int*>(g_noalloc_scratch);
+    const int i = threadIdx.x;
+    if (i < nt) {
+        tab[i] = 0;
+        tab[nt + i] = nt - 1;
+    }
+}
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};   // DEVICE address of g_noalloc_scratch, per device (the symbol's name is
+                                                   // only a host-side stand-in in host code)
+
+// once per device, with that device current
+cudaError_t noalloc_scratch_address(int device, double** out) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        double* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return cudaSuccess;
+}
+}  // namespace
+
+extern "C" int bi_loglikelihood_noalloc(bi_handle h, const double* dy, const double* cov, int64_t n, int32_t Fdim, double* out,
+                                        int32_t* info_out, void* stream) {
+    if (!h || !dy || !cov || !out || n < 0 || Fdim <= 0) return fail(h, BI_E_ARG, "bad argument");
+    if (Fdim > BI_NOALLOC_MAX_F)
+        return fail(h, BI_E_UNSUPPORTED, "bi_loglikelihood_noalloc: F exceeds BI_NOALLOC_MAX_F = 256 (static scratch); use bi_loglikelihood_host");
+    if (n > (int64_t)1 << 40) return fail(h, BI_E_UNSUPPORTED, "bi_loglikelihood_noalloc: n exceeds 2^40 rows");
+    if (n == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    const int F = Fdim, nt = (F + 31) / 32, Fp = nt * 32;
+    const size_t smem = chol_smem_bytes(Fp, 4);
+    CK(raise_explicit_smem(smem));
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_loglik_kernel<true>, CHOL_THREADS, smem));
+    if (occ < 1) return fail(h, BI_E_UNSUPPORTED, "matrix too large for the Cholesky kernel's shared memory");
+    double* scratch = nullptr;
+    CK(noalloc_scratch_address(h->device, &scratch));
+    const long long stride = chol_ws_doubles(nt);              // <= 36,864 doubles at nt = 8
+    const long long fit = BI_NOALLOC_WS_DOUBLES / stride;      // CTAs the fixed scratch can serve (>= 28)
+    const int ctas = (int)std::min<long long>(std::min<long long>(n, fit), (long long)h->sm_count * occ);
+    cudaStream_t s = (cudaStream_t)stream;
+    noalloc_table_kernel<<<1, 32, 0, s>>>(nt);
+    h->launches++;
+    CK(cudaGetLastError());
+    int* tab = reinterpret_cast<int*>(scratch);
+    CholParams P;
+    std::memset(&P, 0, sizeof(P));
+    P.F = F; P.Fp = Fp; P.nt = nt; P.K0 = 4; P.nks0 = 1; P.Ptot = 0; P.d = h->d; P.W = n;
+    P.kmin = tab; P.imax = tab + nt; P.ws = scratch + BI_NOALLOC_TABLE_DOUBLES; P.ws_stride = stride;
+    P.logp = out; P.info = info_out; P.cov_x = cov; P.dy_x = dy;
+    chol_loglik_kernel<true><<<ctas, CHOL_THREADS, smem, s>>>(P);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}

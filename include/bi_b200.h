@@ -13,6 +13,7 @@
  *   emulation.predict (merged)               emulation.py:410-462  bi_predict[_host]
  *   log_posterior.log_posterior              log_posterior.py:42   bi_log_posterior[_host]
  *   log_posterior._loglikelihood             log_posterior.py:104  bi_loglikelihood_host
+ *   (none: operators' request, allocation-free variant)            bi_loglikelihood_noalloc
  *   emcee stretch move driven by mcmc.run_mcmc  mcmc.py:83-107     bi_stretch_propose / bi_stretch_accept
  *   GaussianProcessRegressor.fit objective   emulation.py:169-172  bi_trainer_lml / bi_trainer_factor
  *
@@ -159,6 +160,20 @@ int bi_log_posterior_host(bi_handle h, const double* theta, int64_t W, double n_
  * log_posterior.py:104-146.  F' is arbitrary (need not equal the handle's F). */
 int bi_loglikelihood_host(bi_handle h, const double* dy, const double* cov, int64_t n, int32_t Fdim,
                           double* out, int32_t* info_out);
+
+/* The same log-likelihood for callers that may not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference: added at the request of the run's operators.
+ * dy (n, F'), cov (n, F', F'), out (n) and info_out (n, or NULL) are DEVICE pointers owned by the caller on the handle's
+ * device; the call enqueues two kernels on `stream` and returns without synchronising.  It calls no cudaMalloc /
+ * cudaFree: the kernel's scratch is a file-scope device array of BI_NOALLOC_SCRATCH_BYTES (8 MiB + 256 B) that every
+ * GPU loading the library holds until exit.  Limits: F' <= BI_NOALLOC_MAX_F (256), else BI_E_UNSUPPORTED; n is only
+ * bounded by the caller's buffers (the fixed scratch serves at most 8 MiB / scratch-per-CTA resident CTAs, which loop
+ * over the rows).  All calls, from every handle on a device, share the one array: calls that overlap on the GPU
+ * (different streams without an ordering between them) race; calls ordered on one stream are safe, and nothing in the
+ * array has to be cleared between calls (every tile is written before it is read). */
+#define BI_NOALLOC_MAX_F 256
+int bi_loglikelihood_noalloc(bi_handle h, const double* dy, const double* cov, int64_t n, int32_t Fdim,
+                             double* out, int32_t* info_out, void* stream);
 
 /* ---- the sampler step around the log-posterior (mcmc.py:83-107 -> emcee 3.1.4 RedBlueMove.propose / StretchMove) ----
  * One half-step of the stretch move on device-resident state; everything drawn from the random stream (split, zz,
