@@ -193,6 +193,9 @@ __device__ __forceinline__ void gp_k1_loop(double* sA, const double* sX, const d
 #define GP_K2_NF 2
 #endif
 constexpr int GP_K2_OWNERS = 16 / GP_K2_NF;   // fragment-group owners per 32 walkers = rows of sSq / sMn
+#ifndef GP_K2_DEEP
+#define GP_K2_DEEP 3                          // narrow tiles: groups of k-steps in flight ahead of the DMMAs (0 = shallow loop)
+#endif
 
 template <int GP_WT>
 __device__ __forceinline__ void gp_k2_tile(const PcDesc& pc, const double* sA, int warp, int lane, double* sSq, double* sMn) {
@@ -322,6 +325,136 @@ __device__ __forceinline__ void gp_k2_tile(const PcDesc& pc, const double* sA, i
     }
 }
 
+// K2 for the narrow tiles (8 and 16 walkers per CTA): the same contraction, the same fragment groups per warp and the same
+// order of DMMAs per accumulator as gp_k2_tile (hence the same bits), but the stream of L^-1 runs PF groups of 4 k-steps
+// ahead of the DMMAs through a ring of PF + 1 register buffers instead of one group ahead.  A narrow tile issues 8 or 16
+// DMMAs per group and warp -- 128 to 256 cycles of the FP64 pipe against an L2 round trip of ~340 (in-kernel clock64, C1,
+// 50 walkers: K2 10.1 k cycles of a CTA's 16 k, i.e. one exposed round trip per group) -- so one group ahead leaves the
+// loop latency bound; the wide tiles (32 DMMAs per group, 16 warps per SM) are pipe bound and keep the shallow version,
+// whose 127 registers have no room for a deeper ring.
+template <int GP_WT, int PF>
+__device__ __forceinline__ void gp_k2_tile_deep(const PcDesc& pc, const double* sA, int warp, int lane, double* sSq, double* sMn) {
+    constexpr int NF = GP_K2_NF, NO = GP_K2_OWNERS, R = PF + 1;
+    constexpr int MI = GP_WT / 8;           // m-fragments (8 walkers each) per warp; every warp is a fragment-group owner
+    static_assert(GP_WT == 8 || GP_WT == 16, "narrow tiles only");
+    const int N = pc.N, nks = pc.nks;
+    const int wn = warp;
+    const int g = lane >> 2, t = lane & 3;
+    double sumsq[MI], meanv[MI];
+#pragma unroll
+    for (int mi = 0; mi < MI; ++mi) sumsq[mi] = meanv[mi] = 0.0;
+    const double* sAw = sA + lane;
+    const double* Bl = pc.LinvF + lane;
+    const int kfull = (N + 3) >> 2;
+    const int ftop = N >> 3;
+    const int ngroups = (ftop + NF) / NF;
+    auto klim_of = [&](int f) { return f < 0 ? 0 : min(kfull, 2 * f + 2); };
+
+    struct Cursor { int idx, f0, ngrp, grp; bool valid; };
+    auto seek = [&](Cursor& c) {            // position c on the first k-step group of its idx-th fragment group
+        const int blk = c.idx >> 1;
+        const int q = blk * 2 * NO + ((c.idx & 1) ? 2 * NO - 1 - wn : wn);
+        c.valid = q < ngroups;
+        c.f0 = ftop - NF * q;
+        c.ngrp = c.valid ? (klim_of(c.f0) + 3) >> 2 : 0;
+        c.grp = 0;
+    };
+    auto advance = [&](Cursor& c) {
+        if (++c.grp == c.ngrp) { ++c.idx; seek(c); }
+    };
+    auto load_group = [&](double (&bb)[4][NF], const Cursor& c) {
+#pragma unroll
+        for (int nf = 0; nf < NF; ++nf) {
+            const double* bp = Bl + ((size_t)max(c.f0 - nf, 0) * nks + 4 * c.grp) * 32;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) bb[kk][nf] = __ldg(bp + kk * 32);
+        }
+    };
+
+    Cursor cc{0, 0, 0, 0, false}, cp{0, 0, 0, 0, false};
+    seek(cc);
+    cp = cc;
+    double buf[R][4][NF];
+#pragma unroll
+    for (int s = 0; s < PF; ++s)
+        if (cp.valid) { load_group(buf[s], cp); advance(cp); }
+    double acc[MI][NF][2];
+    while (cc.valid) {
+#pragma unroll
+        for (int s = 0; s < R; ++s) {
+            if (!cc.valid) break;
+            if (cp.valid) { load_group(buf[(s + PF) % R], cp); advance(cp); }
+            const int f0 = cc.f0, grp = cc.grp;
+            if (grp == 0) {
+#pragma unroll
+                for (int mi = 0; mi < MI; ++mi)
+#pragma unroll
+                    for (int nf = 0; nf < NF; ++nf) acc[mi][nf][0] = acc[mi][nf][1] = 0.0;
+            }
+            if (4 * grp + 4 <= klim_of(f0 - (NF - 1))) {
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                    double a[MI];
+#pragma unroll
+                    for (int mi = 0; mi < MI; ++mi) a[mi] = sAw[(mi * nks + grp * 4 + kk) * 32];
+#pragma unroll
+                    for (int mi = 0; mi < MI; ++mi)
+#pragma unroll
+                        for (int nf = 0; nf < NF; ++nf) dmma(acc[mi][nf], a[mi], buf[s][kk][nf]);
+                }
+            } else {
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                    const int ks = grp * 4 + kk;
+                    double a[MI];
+#pragma unroll
+                    for (int mi = 0; mi < MI; ++mi) a[mi] = sAw[(mi * nks + ks) * 32];
+#pragma unroll
+                    for (int nf = 0; nf < NF; ++nf)
+                        if (ks < klim_of(f0 - nf)) {
+#pragma unroll
+                            for (int mi = 0; mi < MI; ++mi) dmma(acc[mi][nf], a[mi], buf[s][kk][nf]);
+                        }
+                }
+            }
+            if (grp == cc.ngrp - 1) {          // the fragment group is complete: fold it into the sums
+                if (f0 == ftop) {
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int n = f0 * 8 + 2 * t + e;
+#pragma unroll
+                        for (int mi = 0; mi < MI; ++mi) {
+                            const double x = acc[mi][0][e];
+                            if (n < N) sumsq[mi] = fma(x, x, sumsq[mi]);
+                            else if (n == N) meanv[mi] = x;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int nf = 0; nf < NF; ++nf) {
+                    if (f0 - nf < 0 || (nf == 0 && f0 == ftop)) continue;
+#pragma unroll
+                    for (int mi = 0; mi < MI; ++mi)
+                        sumsq[mi] = fma(acc[mi][nf][0], acc[mi][nf][0], fma(acc[mi][nf][1], acc[mi][nf][1], sumsq[mi]));
+                }
+            }
+            advance(cc);
+        }
+    }
+#pragma unroll
+    for (int mi = 0; mi < MI; ++mi) {
+        sumsq[mi] += __shfl_xor_sync(0xffffffffu, sumsq[mi], 1);
+        sumsq[mi] += __shfl_xor_sync(0xffffffffu, sumsq[mi], 2);
+        meanv[mi] += __shfl_xor_sync(0xffffffffu, meanv[mi], 1);
+        meanv[mi] += __shfl_xor_sync(0xffffffffu, meanv[mi], 2);
+        if (t == 0) {
+            const int row = mi * 8 + g;
+            sSq[wn * GP_WT + row] = sumsq[mi];
+            sMn[wn * GP_WT + row] = meanv[mi];
+        }
+    }
+}
+
 // var = diag - sum V^2 clipped at 0, std -> squared, mean: thread tid < GP_WT finishes walker w0 + tid
 template <int GP_WT>
 __device__ __forceinline__ void gp_finish_tile(const PcDesc& pc, const double* sSq, const double* sMn, int tid, long long w0, long long W,
@@ -345,17 +478,15 @@ __device__ __forceinline__ void gp_finish_tile(const PcDesc& pc, const double* s
     }
 }
 
-// grid: (ceil(W / GP_WT), n_pc_selected).  pcs[blockIdx.y + pc_first] describes the PC.
+// One (walker tile, PC) unit: walkers w0 .. w0 + GP_WT - 1 against principal component `col` (an index into pcs).
 // k_out (optional): (W, k_ld_pc, N) row-major slice for this group, PC index = desc.local.
-// m_out / v_out (optional): (W, Ptot) at column blockIdx.y + pc_first.
+// m_out / v_out (optional): (W, Ptot) at column col.
 template <bool DO_GP, int GP_WT>
-__global__ void __launch_bounds__(gp_threads(GP_WT), GP_WT <= 32 ? 2 : 1) gp_predict_kernel(const PcDesc* __restrict__ pcs, int pc_first, int d,
-                                                                const double* __restrict__ theta, long long W,
-                                                                double* __restrict__ k_out, int k_npc,
-                                                                double* __restrict__ m_out, double* __restrict__ v_out,
-                                                                int Ptot) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const PcDesc pc = pcs[pc_first + blockIdx.y];
+__device__ __forceinline__ void gp_predict_unit(unsigned char* smem_raw, const PcDesc* __restrict__ pcs, int col, int d,
+                                                const double* __restrict__ theta, long long W, long long w0,
+                                                double* __restrict__ k_out, int k_npc, double* __restrict__ m_out,
+                                                double* __restrict__ v_out, int Ptot) {
+    const PcDesc pc = pcs[col];
     const int N = pc.N, nks = pc.nks;
     double* sA = reinterpret_cast<double*>(smem_raw);
     double* sX = sA + (size_t)GP_WT * 4 * nks;
@@ -365,7 +496,6 @@ __global__ void __launch_bounds__(gp_threads(GP_WT), GP_WT <= 32 ? 2 : 1) gp_pre
 
     constexpr int GP_THREADS = gp_threads(GP_WT), TPW = GP_THREADS / GP_WT;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long w0 = (long long)blockIdx.x * GP_WT;
 #ifdef GP_TIMING
     long long t0_ = clock64();
 #endif
@@ -400,12 +530,52 @@ __global__ void __launch_bounds__(gp_threads(GP_WT), GP_WT <= 32 ? 2 : 1) gp_pre
     GP_T(2);
 
     // ---- K2 -------------------------------------------------------------------------------------------------
+#if GP_K2_DEEP > 0
+    if constexpr (GP_WT <= 16) gp_k2_tile_deep<GP_WT, GP_K2_DEEP>(pc, sA, warp, lane, sSq, sMn);
+    else
+#endif
     gp_k2_tile<GP_WT>(pc, sA, warp, lane, sSq, sMn);
     GP_T(3);
     __syncthreads();
     GP_T(4);
-    gp_finish_tile<GP_WT>(pc, sSq, sMn, tid, w0, W, m_out, v_out, Ptot, pc_first + blockIdx.y);
+    gp_finish_tile<GP_WT>(pc, sSq, sMn, tid, w0, W, m_out, v_out, Ptot, col);
 }
 
+// grid: (ceil(W / GP_WT), n_pc_selected).  pcs[blockIdx.y + pc_first] describes the PC.
+template <bool DO_GP, int GP_WT>
+__global__ void __launch_bounds__(gp_threads(GP_WT), GP_WT <= 32 ? 2 : 1) gp_predict_kernel(const PcDesc* __restrict__ pcs, int pc_first, int d,
+                                                                const double* __restrict__ theta, long long W,
+                                                                double* __restrict__ k_out, int k_npc,
+                                                                double* __restrict__ m_out, double* __restrict__ v_out,
+                                                                int Ptot) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    gp_predict_unit<DO_GP, GP_WT>(smem_raw, pcs, pc_first + blockIdx.y, d, theta, W, (long long)blockIdx.x * GP_WT, k_out, k_npc,
+                                  m_out, v_out, Ptot);
+}
+
+// Mixed tiles in ONE launch (the wave tail): 1024 walkers x 30 PCs in 32-walker tiles are 960 CTAs on 296 resident slots =
+// 3.24 waves, i.e. a fourth wave that is a quarter full.  Here the first n_big walker tiles are 32 walkers wide and the
+// remaining walkers go in tiles of GP_WT_TAIL = 16; CTAs are dealt in block order, big ones first (for each PC its tiles,
+// so that the CTAs resident together share the PC's L^-1 in L2), then the small ones, which fill the slots the last big
+// wave leaves free and halve the length of what runs after it.  Same arithmetic per (walker, PC) and the same summation
+// order in every tile width, hence bit-identical (m, v) to gp_predict_kernel.
+constexpr int GP_WT_TAIL = 16;
+__global__ void __launch_bounds__(256, 2) gp_predict_mixed_kernel(const PcDesc* __restrict__ pcs, int n_pc, int d,
+                                                                  const double* __restrict__ theta, long long W, int n_big,
+                                                                  int n_small, double* __restrict__ m_out,
+                                                                  double* __restrict__ v_out, int Ptot) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int big_units = n_big * n_pc;
+    int u = (int)blockIdx.x;
+    if (u < big_units) {
+        const int col = u / n_big, tile = u - col * n_big;
+        gp_predict_unit<true, 32>(smem_raw, pcs, col, d, theta, W, (long long)tile * 32, nullptr, 0, m_out, v_out, Ptot);
+    } else {
+        u -= big_units;
+        const int col = u / n_small, tile = u - col * n_small;
+        gp_predict_unit<true, GP_WT_TAIL>(smem_raw, pcs, col, d, theta, W, (long long)n_big * 32 + (long long)tile * GP_WT_TAIL, nullptr,
+                                          0, m_out, v_out, Ptot);
+    }
+}
 
 }  // namespace bi

@@ -382,6 +382,39 @@ def test_few_tile_instantiation_equals_main_instantiation(monkeypatch):
     assert rel_err(struct[fin], out[None][fin]) < TOL_LOGP
 
 
+def test_mixed_tile_gp_launch_equals_plain_launch_and_oracle(monkeypatch):
+    # K1+K2 with a partly empty last wave runs 32-walker tiles for the whole waves and 16-walker tiles for the rest in one
+    # launch (gp_predict_mixed_kernel): the same arithmetic per (walker, PC), so (m, v) are bit-identical to the plain
+    # launch for the automatic choice, for forced splits (BI_GP_MIXED=-n) and for ragged batch sizes; and equal to the oracle
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    a = synthetic.generate("C1", n_walkers=1100)
+    img = image.pack(a.emulation_config, a.emulation_results, min=a.min, max=a.max,
+                     experimental_results=a.experimental_results)
+    sizes = (333, 512, 700, 1024, 1061, 1100)
+    out = {}
+    for flag in ("0", None, "-1", "-7", "-1000"):
+        if flag is None:
+            monkeypatch.delenv("BI_GP_MIXED", raising=False)
+        else:
+            monkeypatch.setenv("BI_GP_MIXED", flag)
+        with DeviceEmulator(img, max_batch=1100) as dev:
+            out[flag] = [dev.predict_pc(a.theta[:W]) for W in sizes]
+            if flag is None:
+                lp = dev.log_posterior(a.theta[:700], n_div=1.0, mode="structured")
+    for flag in (None, "-1", "-7", "-1000"):
+        for (m0, v0), (m1, v1), W in zip(out["0"], out[flag], sizes):
+            assert np.array_equal(m0, m1) and np.array_equal(v0, v1), (flag, W)
+    z = img.to_flat()
+    th = a.theta[1040:1100]                          # rows that sit in the 16-walker tiles of the automatic split
+    mo, vo = [np.concatenate(x, axis=1) for x in zip(*[cf.predict_pc(z, g, th) for g in range(len(img.groups))])]
+    m, v = out[None][-1]
+    assert np.max(np.abs(m[1040:] - mo)) < TOL_PC * max(1.0, np.max(np.abs(mo)))
+    assert np.max(np.abs(v[1040:] - vo)) < TOL_PC * 4.0
+    idx = np.flatnonzero(np.isfinite(lp))[:16]
+    _cmp_logp(lp[idx], cf.log_posterior(z, a.theta[idx], n_div=1.0))
+
+
 @pytest.mark.parametrize("name", ["TOY", "C1", "C3B"])
 def test_covariance_kernels_agree(name, monkeypatch):
     # predict(): the persistent per-warp kernel (T resident in shared memory) and the (row tile, walker) grid kernel are
