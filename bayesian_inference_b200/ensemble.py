@@ -189,28 +189,34 @@ def draw_stretch_randoms(rng: np.random.RandomState, nwalkers: int, ndim: int, n
     accept test compares exactly the numbers the host sampler compares.
     """
     W, ns = nwalkers, nwalkers // 2
-    # the loop only draws (the order of the draws is what must be preserved); everything else is vectorised after it
-    inds_all = np.empty((nsteps, W), np.int64)
+    # the loop only draws (the order of the draws is what must be preserved); everything else is vectorised after it.
+    # At 8192 walkers this host work is what bounds an ensemble sharded over 8 GPUs (0.9 ms per half-step before it was
+    # trimmed: uint8 split labels shuffled in place, the halves by a stable radix argsort instead of two nonzero scans)
+    inds_all = np.empty((nsteps, W), np.uint8)
     u_zz, u_acc = np.empty((nsteps, 2, ns)), np.empty((nsteps, 2, ns))
     rint = np.empty((nsteps, 2, ns), np.int64)
-    base = np.arange(W) % 2
+    inds_all[:] = (np.arange(W) % 2).astype(np.uint8)
     for t in range(nsteps):
         rng.random_sample()
-        inds = base.copy()
-        rng.shuffle(inds)
-        inds_all[t] = inds
+        rng.shuffle(inds_all[t])            # the swaps depend on the stream and the length only, not on the element type
         for split in range(2):
             u_zz[t, split] = rng.rand(ns)
             rint[t, split] = rng.randint(W - ns, size=(ns,))
             u_acc[t, split] = rng.rand(ns)
-    ids = [np.nonzero(inds_all == split)[1].reshape(nsteps, ns) for split in range(2)]   # walkers of each half, ascending
-    s_idx = np.stack([ids[0], ids[1]], axis=1)
-    c_ids = np.stack([ids[1], ids[0]], axis=1)
+    order = np.argsort(inds_all, axis=1, kind="stable")    # walkers of half 0 ascending, then those of half 1
+    n0 = W - ns                                            # half 0 has one walker more when W is odd
+    if n0 != ns:
+        raise ValueError("the device-side stretch move needs an even number of walkers")
+    s_idx = np.empty((nsteps, 2, ns), np.int32)
+    s_idx[:, 0], s_idx[:, 1] = order[:, :n0], order[:, n0:]
+    # partners: walker ids of the complementary half, picked by rint -- one flat take instead of take_along_axis
+    comp = s_idx[:, ::-1].reshape(-1)
+    rint += (np.arange(nsteps * 2, dtype=np.int64) * ns).reshape(nsteps, 2, 1)
+    c_idx = comp.take(rint)
     zz = ((a - 1.0) * u_zz + 1.0) ** 2.0 / a
     with np.errstate(divide="ignore"):
-        logu = np.log(u_acc)
-    return {"s_idx": s_idx.astype(np.int32), "c_idx": np.take_along_axis(c_ids, rint, axis=2).astype(np.int32),
-            "zz": zz, "factors": (ndim - 1.0) * np.log(zz), "logu": logu}
+        logu = np.log(u_acc, out=u_acc)
+    return {"s_idx": s_idx, "c_idx": c_idx, "zz": zz, "factors": (ndim - 1.0) * np.log(zz), "logu": logu}
 
 
 class DeviceStretchEnsemble(StretchEnsemble):

@@ -107,6 +107,16 @@ def main():
         philox = [pre + n for n in names if "philox" in n]
         if philox:
             out[pre + "identical_chain_philox"] = len({sums[n] for n in philox}) <= 1
+    # host side of emcee's stream alone (chain independent, drawn one block ahead while the GPU runs): when it takes longer
+    # than the device's half-step the chain is bound by it, whatever the number of GPUs
+    import time as _time
+
+    from bayesian_inference_b200.ensemble import draw_stretch_randoms
+    _rs = np.random.RandomState(0)
+    draw_stretch_randoms(_rs, W, d, 4)
+    _t0 = _time.perf_counter()
+    draw_stretch_randoms(_rs, W, d, 32)
+    out["host_emcee_stream_us_per_half_step"] = (_time.perf_counter() - _t0) / 64 * 1e6
     if world > 1:
         # the collective alone: the very call of a half-step (W/2 log-probabilities, ceil(W/2/N) per rank), CUDA events
         per = (W // 2 + world - 1) // world
