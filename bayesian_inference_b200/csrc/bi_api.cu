@@ -102,6 +102,7 @@ struct bi_handle_s {
     // block-direct evaluation of BI_MODE_STRUCTURED (every observable block fits one warp: f_b <= 31)
     int bd_state = 0;             // 0 not looked at yet, 1 usable, -1 not applicable (falls back to the tile-skipping kernel)
     int bdFB = 0, bdNks = 0;      // row length padded to a multiple of 8; k-steps of 4 principal components (max over blocks)
+    bool bdAugIn = false;         // every block leaves row FB - 1 free: the augmented row rides inside the last fragment
     std::vector<BdBlock> bdBlocks;
     BdBlock* dBdBlocks = nullptr;
     double* dBdA[2] = {nullptr, nullptr};      // [0] n_div = 1 (never rewritten), [1] the last other divisor
@@ -1170,11 +1171,16 @@ static int ensure_block_direct(bi_handle h) {
     if (block_direct_smem_bytes(h->bdFB, h->bdNks) > 113 * 1024) return 0;   // two CTAs per SM must fit (108.7 KB at FB = 32, P = 64)
     {
         cudaError_t e_ = cudaSuccess;
-        switch (h->bdFB) {
-            case 8: e_ = allow_max_smem(block_direct_kernel<8>); break;
-            case 16: e_ = allow_max_smem(block_direct_kernel<16>); break;
-            case 24: e_ = allow_max_smem(block_direct_kernel<24>); break;
-            default: e_ = allow_max_smem(block_direct_kernel<32>); break;
+        h->bdAugIn = fmax < h->bdFB;   // a free row in the last fragment for the augmented row
+        if (const char* e = std::getenv("BI_BD_AUGIN")) h->bdAugIn = h->bdAugIn && std::atoi(e) != 0;   // developer A/B knob
+        switch (h->bdFB + (h->bdAugIn ? 1 : 0)) {
+            case 8: e_ = allow_max_smem(block_direct_kernel<8, false>); break;
+            case 9: e_ = allow_max_smem(block_direct_kernel<8, true>); break;
+            case 16: e_ = allow_max_smem(block_direct_kernel<16, false>); break;
+            case 17: e_ = allow_max_smem(block_direct_kernel<16, true>); break;
+            case 24: e_ = allow_max_smem(block_direct_kernel<24, false>); break;
+            case 25: e_ = allow_max_smem(block_direct_kernel<24, true>); break;
+            default: e_ = allow_max_smem(block_direct_kernel<32, true>); break;
         }
         if (e_ != cudaSuccess) { h->err = std::string("block_direct smem: ") + cudaGetErrorString(e_); return (int)e_; }
     }
@@ -1224,15 +1230,18 @@ static int run_block_direct(bi_handle h, const double* dTheta, long long W, doub
         const dim3 grid((unsigned)nB, (unsigned)((wb + (long long)BD_WARPS * wpw - 1) / ((long long)BD_WARPS * wpw)));
         {
             ProfScope ps(h, 1, s);
-#define BD_LAUNCH(FBV)                                                                                                       \
-    block_direct_kernel<FBV><<<grid, BD_THREADS, smem, s>>>(h->dBdBlocks, nB, wb, wpw, h->Ptot, h->K0, h->bdNks, h->dM, h->dV, h->dTrow, dEall, \
+#define BD_LAUNCH(FBV, INV)                                                                                                  \
+    block_direct_kernel<FBV, INV><<<grid, BD_THREADS, smem, s>>>(h->dBdBlocks, nB, wb, wpw, h->Ptot, h->K0, h->bdNks, h->dM, h->dV, h->dTrow, dEall, \
                                                             dAall, h->dBdPart, h->dBdBad, dSetId ? dSetId + w0 : nullptr, e_stride,  \
                                                             a_stride)
-            switch (h->bdFB) {
-                case 8: BD_LAUNCH(8); break;
-                case 16: BD_LAUNCH(16); break;
-                case 24: BD_LAUNCH(24); break;
-                default: BD_LAUNCH(32); break;
+            switch (h->bdFB + (h->bdAugIn ? 1 : 0)) {
+                case 8: BD_LAUNCH(8, false); break;
+                case 9: BD_LAUNCH(8, true); break;
+                case 16: BD_LAUNCH(16, false); break;
+                case 17: BD_LAUNCH(16, true); break;
+                case 24: BD_LAUNCH(24, false); break;
+                case 25: BD_LAUNCH(24, true); break;
+                default: BD_LAUNCH(32, true); break;
             }
 #undef BD_LAUNCH
             block_combine_kernel<<<(unsigned)((wb + 127) / 128), 128, 0, s>>>(nB, wb, h->d, dTheta + w0 * h->d, h->dMin, h->dMax,

@@ -9,8 +9,8 @@
 //   * assembly  a[r][c] = A_b[r][c] + sum_p (T[r][p] v_p) T[c][p] on the FP64 tensor pipe (mma.sync m8n8k4): T_b is staged
 //     in shared memory once per CTA as operand fragments (a CTA works on one block for a batch of walkers); only the
 //     lower 8 x 8 tiles are computed; the accumulators go through a per-warp row-major tile to one row per lane;
-//   * lane 31 carries the augmented row dy_b (one more fragment row in the assembly: m in place of T[r][.] v, e_b in place
-//     of A_b[r][.]), so the right-looking elimination turns it into z = L^-1 dy and the quadratic form is sum z^2: no
+//   * one lane carries the augmented row dy_b (m in place of T[r][.] v, e_b in place of A_b[r][.]): lane FB - 1 inside the
+//     last 8-row fragment when every block leaves that row free (f < FB), else lane 31 with a fragment row of its own, so the right-looking elimination turns it into z = L^-1 dy and the quadratic form is sum z^2: no
 //     separate substitution (the device K4 kernels use the same augmentation);
 //   * right-looking Cholesky in registers: the pivot column is broadcast through a double-buffered 32-entry line of shared
 //     memory (the first version used warp shuffles and was bound by the shuffle / load-store unit); rows between f and the
@@ -72,19 +72,23 @@ __host__ __device__ inline size_t block_direct_smem_bytes(int FB, int nks) {
 //     SM's shuffle / load-store unit (ncu: 1073 of 3200 instructions per task, short-scoreboard + MIO-throttle stalls 50 %).
 //     The update uses u = a[r][c] / pivot and the unscaled column, L[r][c] L[c2][c] = u * a[c2][c].
 // Resident CTAs per SM by row length (registers for warps).
-template <int FB>
+// AUGIN: every block has f <= FB - 1, so the augmented row rides in row FB - 1 of the last 8-row fragment (lane FB - 1)
+// instead of a fragment row of its own -- a third fewer DMMAs in the assembly at FB = 24.  FB = 32 is always AUGIN (f <= 31).
+template <int FB, bool AUGIN_>
 __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2)) block_direct_kernel(
     const BdBlock* __restrict__ blocks, int nB, long long W, int wpw, int Ptot, int K0, int nksmax, const double* __restrict__ m,
     const double* __restrict__ v, const double* __restrict__ Trow, const double* __restrict__ e, const double* __restrict__ Aall,
     double* __restrict__ part, int* __restrict__ bad_out, const int* __restrict__ set_id, long long e_stride, long long a_stride) {
     constexpr int NFR = FB / 8;                               // 8-row fragments holding matrix rows
-    constexpr bool AUGF = FB < 32;                            // the augmented row has a fragment row of its own
+    constexpr bool AUGIN = AUGIN_ || FB == 32;
+    constexpr bool AUGF = !AUGIN;                             // the augmented row has a fragment row of its own
     constexpr int LDC = FB + 2;
-    constexpr int NCOL = (FB == 32) ? 31 : FB;                // columns eliminated (column 31 would be the augmented row's own)
-    constexpr int AUGROW = (FB == 32) ? 31 : FB;              // row of sC holding the augmented row
+    constexpr int NCOL = AUGIN ? FB - 1 : FB;                 // columns eliminated (column FB - 1 would be the augmented row's own)
+    constexpr int AUGROW = AUGIN ? FB - 1 : FB;               // row of sC holding the augmented row
+    constexpr int AL = AUGIN ? FB - 1 : 31;                   // lane (= row of sA) that carries the augmented row
     extern __shared__ __align__(16) unsigned char bd_smem[];
     double* sTf = reinterpret_cast<double*>(bd_smem);        // [mf][ks][lane] = T_b[8 mf + g][4 ks + t]
-    double* sA = sTf + (size_t)NFR * nksmax * 32;             // [r][c]  A_b, identity rows f..30, row 31 = e_b
+    double* sA = sTf + (size_t)NFR * nksmax * 32;             // [r][c]  A_b, identity rows f.., row AL = e_b
     double* sW = sA + 32 * FB;                                // per-warp scratch
     const BdBlock B = blocks[blockIdx.x];
     const int f = B.f, P = B.P;
@@ -103,7 +107,7 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
     for (int idx = tid; idx < 32 * FB; idx += BD_THREADS) {
         const int r = idx / FB, c = idx - r * FB;
         double x;
-        if (r == 31) x = (c < f) ? __ldg(e + B.row0 + c) : 0.0;
+        if (r == AL) x = (c < f) ? __ldg(e + B.row0 + c) : 0.0;
         else if (r < f && c < f) x = __ldg(Aall + B.a_off + (size_t)r * f + c);
         else x = (r == c) ? 1.0 : 0.0;
         sA[idx] = x;
@@ -111,7 +115,7 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
     for (int idx = lane; idx < (FB + 1) * LDC; idx += 32) sC[idx] = 0.0;   // tiles above the diagonal are never written
     __syncthreads();
 
-    const bool is_aug = lane == 31;
+    const bool is_aug = lane == AL;
     const bool has_row = lane < FB || is_aug;
     const int nks = (P + 3) >> 2;
     const long long w_base = (long long)blockIdx.y * BD_WARPS * wpw + warp;
@@ -142,7 +146,7 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
                     tf[mf] = sTf[((size_t)mf * nksmax + ks) * 32 + lane];
                     ta[mf] = tf[mf] * vk;
                 }
-                if (!AUGF && g == 7) ta[NFR - 1] = mk;        // FB = 32: row 31 of the last fragment is the augmented row
+                if (!AUGF && g == 7) ta[NFR - 1] = mk;        // row FB - 1 of the last fragment is the augmented row
 #pragma unroll
                 for (int mi = 0; mi < NFR; ++mi)
 #pragma unroll
@@ -224,7 +228,7 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
             }
         }
         const double ld = warp_sum((lane < f) ? 0.5 * log(mypiv) : 0.0);
-        quad = shfl_d(quad, 31);
+        quad = shfl_d(quad, AL);
         if (lane == 0) {
             part[w * nB + blockIdx.x] = bad ? __longlong_as_double(0x7ff8000000000000LL) : (-0.5 * quad - ld);
             bad_out[w * nB + blockIdx.x] = bad ? B.row0 + bad : 0;

@@ -167,6 +167,14 @@ def test_structured_block_direct_equals_tile_skipping_dense_and_oracle(name, W, 
     with DeviceEmulator(img, max_batch=128) as dev2:
         assert dev2.query(18) == 0
         tiles = dev2.log_posterior(a.theta, n_div=1.0, mode="structured")
+    monkeypatch.delenv("BI_STRUCT_IMPL")
+    monkeypatch.setenv("BI_BD_AUGIN", "0")                                # the augmented row in a fragment row of its own
+    with DeviceEmulator(img, max_batch=128) as dev3:
+        assert dev3.query(18) == 1
+        own_row = dev3.log_posterior(a.theta, n_div=1.0, mode="structured")
+    assert np.array_equal(np.isneginf(own_row), np.isneginf(direct))
+    fin = np.isfinite(direct)
+    assert rel_err(own_row[fin], direct[fin]) < 1e-13                    # same products, same elimination of the real columns
     assert np.array_equal(direct, again, equal_nan=True)                 # deterministic (block terms summed in block order)
     assert np.array_equal(one, direct[[0, 5, W - 1]])                    # a walker's value does not depend on its batch
     inside = np.all((a.theta > a.min) & (a.theta < a.max), axis=1)
