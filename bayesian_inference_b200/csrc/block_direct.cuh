@@ -51,9 +51,10 @@ __global__ void __launch_bounds__(256) block_a_kernel(const BdBlock* __restrict_
 }
 
 __host__ __device__ inline size_t block_direct_smem_bytes(int FB, int nks) {
-    // CTA: sTf (T_b as DMMA operand fragments, FB/8 x nks x 32) + sA (32 x FB: A_b rows, identity rows f.., row 31 = e_b)
+    // CTA: sTf (T_b as DMMA operand fragments, FB/8 x nks x 32) + sA (32 x (FB + 2): A_b rows, identity rows f.., one row = e_b;
+    //      the row stride FB + 2 is an odd number of 16-byte words: a lane per row reads it with LDS.128 free of bank conflicts)
     // per warp: sC ((FB+1) x (FB+2): the assembled block, row-major) + sCol (2 x 32: column broadcast) + v and m (2 x 4 nks)
-    return sizeof(double) * ((size_t)(FB / 8) * nks * 32 + (size_t)32 * FB +
+    return sizeof(double) * ((size_t)(FB / 8) * nks * 32 + (size_t)32 * (FB + 2) +
                              (size_t)BD_WARPS * ((size_t)(FB + 1) * (FB + 2) + 64 + 8 * nks));
 }
 
@@ -89,7 +90,7 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
     extern __shared__ __align__(16) unsigned char bd_smem[];
     double* sTf = reinterpret_cast<double*>(bd_smem);        // [mf][ks][lane] = T_b[8 mf + g][4 ks + t]
     double* sA = sTf + (size_t)NFR * nksmax * 32;             // [r][c]  A_b, identity rows f.., row AL = e_b
-    double* sW = sA + 32 * FB;                                // per-warp scratch
+    double* sW = sA + 32 * LDC;                               // per-warp scratch
     const BdBlock B = blocks[blockIdx.x];
     const int f = B.f, P = B.P;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
@@ -110,13 +111,12 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
         if (r == AL) x = (c < f) ? __ldg(e + B.row0 + c) : 0.0;
         else if (r < f && c < f) x = __ldg(Aall + B.a_off + (size_t)r * f + c);
         else x = (r == c) ? 1.0 : 0.0;
-        sA[idx] = x;
+        sA[r * LDC + c] = x;
     }
     for (int idx = lane; idx < (FB + 1) * LDC; idx += 32) sC[idx] = 0.0;   // tiles above the diagonal are never written
     __syncthreads();
 
     const bool is_aug = lane == AL;
-    const bool has_row = lane < FB || is_aug;
     const int nks = (P + 3) >> 2;
     const long long w_base = (long long)blockIdx.y * BD_WARPS * wpw + warp;
     for (int it = 0; it < wpw; ++it) {
@@ -174,12 +174,12 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
         {
             const double2* crow = reinterpret_cast<const double2*>(sC + (is_aug ? AUGROW : (lane < FB ? lane : 0)) * LDC);
             if (set_id == nullptr) {
-                const double2* init = reinterpret_cast<const double2*>(sA + lane * FB);
+                const double2* init = reinterpret_cast<const double2*>(sA + lane * LDC);
 #pragma unroll
                 for (int c = 0; c < FB; c += 2) {
                     const double2 x = init[c >> 1], y = crow[c >> 1];
-                    a[c] = has_row ? x.x + y.x : 0.0;
-                    a[c + 1] = has_row ? x.y + y.y : 0.0;
+                    a[c] = x.x + y.x;                          // lanes that hold no row compute on row 0 / their (unused) sA row:
+                    a[c + 1] = x.y + y.y;                      // nothing of theirs is ever read by another lane
                 }
             } else {
                 // several experimental data sets on one image (closure tests, steer_analysis.py:168-183): A_b and e_b of this
@@ -199,13 +199,12 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
                         if (is_aug) x1 = __ldg(es + c + 1);
                         else if (lane < f) x1 = __ldg(As + c + 1);
                     } else if (is_aug) x1 = 0.0;
-                    a[c] = has_row ? x0 + y.x : 0.0;
-                    a[c + 1] = has_row ? x1 + y.y : 0.0;
+                    a[c] = x0 + y.x;
+                    a[c + 1] = x1 + y.y;
                 }
             }
         }
         // ---- 3. right-looking Cholesky in registers; lane 31 becomes z = L^-1 dy
-        int bad = 0;
         double mypiv = 1.0, quad = 0.0;
 #pragma unroll
         for (int c = 0; c < NCOL; ++c) {
@@ -213,7 +212,6 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
             cb[lane] = a[c];                                  // column c of the current matrix, all rows
             __syncwarp();
             const double piv = cb[c];
-            if (!(piv > 0.0) && bad == 0) bad = c + 1;
             if (lane == c) mypiv = piv;
             const double rinv = rsqrt(piv);
             const double u = a[c] * (rinv * rinv);            // a[r][c] / pivot
@@ -227,6 +225,9 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
                 if (e2 + 1 < NCOL) a[e2 + 1] = fma(-u, l2.y, a[e2 + 1]);
             }
         }
+        // first non-positive pivot (1-based), found after the fact: lane c kept pivot c, and everything behind a bad pivot is NaN
+        const unsigned badmask = __ballot_sync(0xffffffffu, lane < f && !(mypiv > 0.0));
+        const int bad = badmask ? __ffs(badmask) : 0;
         const double ld = warp_sum((lane < f) ? 0.5 * log(mypiv) : 0.0);
         quad = shfl_d(quad, AL);
         if (lane == 0) {
