@@ -289,7 +289,7 @@ def roofline_record(img, spec_name, W, mode, dev, gp, ch, total_ms, traffic):
     if gp_avg >= ch_avg:
         flg = gp_flops_per_eval(img.groups)
         achieved = flg * W / (gp_avg * 1e-3) / 1e12 if gp_n else None
-        rec.update(kernel=f"gp_predict_kernel (K1+K2) -- the dominant kernel of the {mode} step: the factorisation stage is "
+        rec.update(kernel=f"gp_predict_mixed_kernel / gp_predict_kernel (K1+K2) -- the dominant kernel of the {mode} step: the factorisation stage is "
                           f"{ch_avg:.3f} ms of it",
                    achieved=achieved, frac=(achieved / FP64_TENSOR_PEAK_TFLOPS) if achieved else None, flops_per_eval=flg,
                    flops_counting="K2: sum_g P_g (N^2 + 4 N) (SURVEY 8d)", avg_launch_ms=gp_avg, launches_timed=int(gp_n),
