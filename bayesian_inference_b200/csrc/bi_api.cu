@@ -103,6 +103,8 @@ struct bi_handle_s {
     int bd_state = 0;             // 0 not looked at yet, 1 usable, -1 not applicable (falls back to the tile-skipping kernel)
     int bdFB = 0, bdNks = 0;      // row length padded to a multiple of 8; k-steps of 4 principal components (max over blocks)
     bool bdAugIn = false;         // every block leaves row FB - 1 free: the augmented row rides inside the last fragment
+    int* dBdCount = nullptr;      // (max_batch) per-walker count of delivered block terms: the combine step fused into the kernel
+    bool bdFuse = true;           // developer knob BI_BD_FUSE=0: separate block_combine_kernel launch
     std::vector<BdBlock> bdBlocks;
     BdBlock* dBdBlocks = nullptr;
     double* dBdA[2] = {nullptr, nullptr};      // [0] n_div = 1 (never rewritten), [1] the last other divisor
@@ -1190,6 +1192,9 @@ static int ensure_block_direct(bi_handle h) {
         if ((rc = dalloc(h, &h->dBdA[i], (size_t)a_tot))) return rc;
     if ((rc = dalloc(h, &h->dBdPart, (size_t)h->max_batch * nB))) return rc;
     if ((rc = dalloc(h, &h->dBdBad, (size_t)h->max_batch * nB))) return rc;
+    if ((rc = dalloc(h, &h->dBdCount, (size_t)h->max_batch))) return rc;
+    CK(cudaMemsetAsync(h->dBdCount, 0, (size_t)h->max_batch * sizeof(int), h->stream));   // after the guard-mode poison, same stream
+    if (const char* e = std::getenv("BI_BD_FUSE")) h->bdFuse = std::atoi(e) != 0;
     CK(cudaStreamSynchronize(h->stream));
     h->bd_state = 1;
     return 0;
@@ -1228,12 +1233,20 @@ static int run_block_direct(bi_handle h, const double* dTheta, long long W, doub
         const long long tasks = wb * nB;
         int wpw = (int)std::max<long long>(1, std::min<long long>(8, tasks / ((long long)h->sm_count * 2 * BD_WARPS * 4)));
         const dim3 grid((unsigned)nB, (unsigned)((wb + (long long)BD_WARPS * wpw - 1) / ((long long)BD_WARPS * wpw)));
+        // The combine step rides in the block kernel only for launches of at most one wave of (walker, block) tasks (a sampler
+        // half-step of a 100-walker ensemble): there it saves a launch (C1, 100 walkers: 18.9 -> 15.9 us); on a full batch
+        // the serial tail and the fences cost more than the 3 us kernel they replace (C3a, 1024 walkers: 0.103 -> 0.113 ms).
+        const bool fuse_now = h->bdFuse && tasks <= (long long)h->sm_count * 3 * BD_WARPS;
+        BdFuse fuse;
+        fuse.counter = fuse_now ? h->dBdCount : nullptr;
+        fuse.theta = dTheta + w0 * h->d; fuse.lo = h->dMin; fuse.hi = h->dMax; fuse.logp = dLogp + w0;
+        fuse.info = dInfo ? dInfo + w0 : nullptr; fuse.d = h->d;
         {
             ProfScope ps(h, 1, s);
 #define BD_LAUNCH(FBV, INV)                                                                                                  \
     block_direct_kernel<FBV, INV><<<grid, BD_THREADS, smem, s>>>(h->dBdBlocks, nB, wb, wpw, h->Ptot, h->K0, h->bdNks, h->dM, h->dV, h->dTrow, dEall, \
                                                             dAall, h->dBdPart, h->dBdBad, dSetId ? dSetId + w0 : nullptr, e_stride,  \
-                                                            a_stride)
+                                                            a_stride, fuse)
             switch (h->bdFB + (h->bdAugIn ? 1 : 0)) {
                 case 8: BD_LAUNCH(8, false); break;
                 case 9: BD_LAUNCH(8, true); break;
@@ -1244,11 +1257,12 @@ static int run_block_direct(bi_handle h, const double* dTheta, long long W, doub
                 default: BD_LAUNCH(32, true); break;
             }
 #undef BD_LAUNCH
-            block_combine_kernel<<<(unsigned)((wb + 127) / 128), 128, 0, s>>>(nB, wb, h->d, dTheta + w0 * h->d, h->dMin, h->dMax,
-                                                                              h->dBdPart, h->dBdBad, dLogp + w0,
-                                                                              dInfo ? dInfo + w0 : nullptr);
+            if (!fuse_now)
+                block_combine_kernel<<<(unsigned)((wb + 127) / 128), 128, 0, s>>>(nB, wb, h->d, dTheta + w0 * h->d, h->dMin, h->dMax,
+                                                                                  h->dBdPart, h->dBdBad, dLogp + w0,
+                                                                                  dInfo ? dInfo + w0 : nullptr);
         }
-        h->launches += 2;
+        h->launches += fuse_now ? 1 : 2;
         CK(cudaGetLastError());
     }
     return 0;

@@ -32,6 +32,17 @@ struct BdBlock {
     long long a_off;  // offset (doubles) of this block's f x f matrix A_b in the per-divisor array
 };
 
+// the combine step fused into block_direct_kernel (counter == nullptr: separate block_combine_kernel launch)
+struct BdFuse {
+    int* counter;             // (max_batch) zero between launches: block terms delivered per walker
+    const double* theta;      // (W, d)
+    const double* lo;         // (d) strict prior box
+    const double* hi;
+    double* logp;             // (W)
+    int* info;                // (W) or nullptr
+    int d;
+};
+
 constexpr int BD_WARPS = 8;
 constexpr int BD_THREADS = BD_WARPS * 32;
 constexpr int BD_PMAX = 64;    // principal components per group the staging buffers hold
@@ -79,7 +90,8 @@ template <int FB, bool AUGIN_>
 __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2)) block_direct_kernel(
     const BdBlock* __restrict__ blocks, int nB, long long W, int wpw, int Ptot, int K0, int nksmax, const double* __restrict__ m,
     const double* __restrict__ v, const double* __restrict__ Trow, const double* __restrict__ e, const double* __restrict__ Aall,
-    double* __restrict__ part, int* __restrict__ bad_out, const int* __restrict__ set_id, long long e_stride, long long a_stride) {
+    double* __restrict__ part, int* __restrict__ bad_out, const int* __restrict__ set_id, long long e_stride, long long a_stride,
+    const BdFuse fuse) {
     constexpr int NFR = FB / 8;                               // 8-row fragments holding matrix rows
     constexpr bool AUGIN = AUGIN_ || FB == 32;
     constexpr bool AUGF = !AUGIN;                             // the augmented row has a fragment row of its own
@@ -230,9 +242,36 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
         const int bad = badmask ? __ffs(badmask) : 0;
         const double ld = warp_sum((lane < f) ? 0.5 * log(mypiv) : 0.0);
         quad = shfl_d(quad, AL);
+        int last = 0;
         if (lane == 0) {
             part[w * nB + blockIdx.x] = bad ? __longlong_as_double(0x7ff8000000000000LL) : (-0.5 * quad - ld);
             bad_out[w * nB + blockIdx.x] = bad ? B.row0 + bad : 0;
+            if (fuse.counter != nullptr) {
+                __threadfence();                                            // this block's term is visible before the count
+                last = atomicAdd(fuse.counter + w, 1) == nB - 1;
+            }
+        }
+        // the warp that delivers a walker's last block term adds the terms up, in block order (deterministic whichever warp
+        // that is), applies the strict prior box and re-arms the counter for the next launch: no combine kernel
+        if (__shfl_sync(0xffffffffu, last, 0)) {
+            if (lane == 0) {
+                __threadfence();
+                bool inside = true;
+                for (int k = 0; k < fuse.d; ++k) {
+                    const double x = fuse.theta[w * fuse.d + k];
+                    if (!(x > fuse.lo[k] && x < fuse.hi[k])) inside = false;
+                }
+                double sum = 0.0;
+                int first_bad = 0;
+                for (int b = 0; b < nB; ++b) {
+                    sum += __ldcg(part + w * nB + b);                       // L2: the terms come from other SMs
+                    const int bb = __ldcg(bad_out + w * nB + b);
+                    if (bb != 0 && first_bad == 0) first_bad = bb;
+                }
+                fuse.logp[w] = inside ? sum : -INFINITY;
+                if (fuse.info) fuse.info[w] = inside ? first_bad : -1;
+                fuse.counter[w] = 0;
+            }
         }
     }
 }
