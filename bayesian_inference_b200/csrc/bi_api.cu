@@ -41,6 +41,21 @@ cudaError_t allow_max_smem(Kernel* kernel) {
     return e;
 }
 
+// Launch with (pdl) or without the programmatic-serialisation attribute (common.cuh pdl_wait / pdl_trigger): the kernels of a
+// sampler half-step -- propose, K1+K2, K5 direct, combine, accept -- start while their predecessor drains and run their
+// theta-independent prologue (staging of X / ell, of T_b and A_b) ahead of it.  Captured as a programmatic edge in a CUDA graph.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_k(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 struct GroupImg {
     int N = 0, P = 0, Fg = 0, R = 0, nks = 0, ntn = 0, K0g = 0, pc_off = 0;
     double* dXsT = nullptr;    // (P, d, N)
@@ -127,6 +142,7 @@ struct bi_handle_s {
     size_t chol_smem = 0, gp_smem = 0;
     int gp_wt = 32;
     int gp_small = 1;         // 8-walker tiles for launches of less than one wave (developer knob BI_GP_SMALL=0 switches it off)
+    bool pdl = true;          // programmatic dependent launch for the half-step kernels (developer knob BI_PDL=0 switches it off)
     int gp_mixed = 1;         // 32 + 16-walker tiles in one launch when the last wave is partly empty (BI_GP_MIXED: 0 off,
                               // 1 auto, -n forces n 32-walker tiles)
     int k3_persist = -1;      // covariance assembly: -1 = choose per layout, 0 / 1 = developer override (BI_K3_PERSIST)
@@ -295,13 +311,16 @@ int launch_gp(bi_handle h, const double* dTheta, long long W, double* dM, double
         if (n_big >= 0) {
             const long long n_small = (W - 32 * n_big + GP_WT_TAIL - 1) / GP_WT_TAIL;
             grid = dim3((unsigned)((n_big + n_small) * h->Ptot), 1);
-            gp_predict_mixed_kernel<<<grid, 256, h->gp_smem, s>>>(h->dPcs, h->Ptot, h->d, dTheta, W, (int)n_big, (int)n_small, dM, dV, h->Ptot);
+            CK(launch_k(h->pdl, gp_predict_mixed_kernel, grid, dim3(256), h->gp_smem, s, h->dPcs, h->Ptot, h->d, dTheta, W, (int)n_big,
+                        (int)n_small, dM, dV, h->Ptot));
         } else if (wt == 64)
             gp_predict_kernel<true, 64><<<grid, 512, h->gp_smem, s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
         else if (wt == 8)
-            gp_predict_kernel<true, 8><<<grid, gp_threads(8), gp_smem_bytes(h->d, h->Nmax, 8), s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
+            CK(launch_k(h->pdl, gp_predict_kernel<true, 8>, grid, dim3(gp_threads(8)), gp_smem_bytes(h->d, h->Nmax, 8), s, h->dPcs, 0, h->d,
+                        dTheta, W, (double*)nullptr, 0, dM, dV, h->Ptot));
         else
-            gp_predict_kernel<true, 32><<<grid, 256, h->gp_smem, s>>>(h->dPcs, 0, h->d, dTheta, W, nullptr, 0, dM, dV, h->Ptot);
+            CK(launch_k(h->pdl, gp_predict_kernel<true, 32>, grid, dim3(256), h->gp_smem, s, h->dPcs, 0, h->d, dTheta, W, (double*)nullptr, 0,
+                        dM, dV, h->Ptot));
 #ifdef GP_TIMING
         {
             unsigned long long z[8];
@@ -806,6 +825,7 @@ int bi_create(const bi_desc* D, bi_handle* out) {
     if (const char* e = std::getenv("BI_GP_WT")) h->gp_wt = std::atoi(e) == 64 ? 64 : 32;   // developer A/B knob
     if (const char* e = std::getenv("BI_GP_SMALL")) h->gp_small = std::atoi(e);   // 0 off, 16: 16-walker tiles, else 8-walker tiles
     if (const char* e = std::getenv("BI_GP_MIXED")) h->gp_mixed = std::atoi(e);
+    if (const char* e = std::getenv("BI_PDL")) h->pdl = std::atoi(e) != 0;
     if (gp_smem_bytes(d, h->Nmax, h->gp_wt) > 227 * 1024) h->gp_wt = 32;
     h->gp_smem = gp_smem_bytes(d, h->Nmax, h->gp_wt);
     if (h->gp_smem > 227 * 1024) {
@@ -1244,9 +1264,9 @@ static int run_block_direct(bi_handle h, const double* dTheta, long long W, doub
         {
             ProfScope ps(h, 1, s);
 #define BD_LAUNCH(FBV, INV)                                                                                                  \
-    block_direct_kernel<FBV, INV><<<grid, BD_THREADS, smem, s>>>(h->dBdBlocks, nB, wb, wpw, h->Ptot, h->K0, h->bdNks, h->dM, h->dV, h->dTrow, dEall, \
-                                                            dAall, h->dBdPart, h->dBdBad, dSetId ? dSetId + w0 : nullptr, e_stride,  \
-                                                            a_stride, fuse)
+    CK(launch_k(h->pdl, block_direct_kernel<FBV, INV>, grid, dim3(BD_THREADS), smem, s, h->dBdBlocks, nB, wb, wpw, h->Ptot, h->K0,       \
+                h->bdNks, h->dM, h->dV, h->dTrow, dEall, dAall, h->dBdPart, h->dBdBad, dSetId ? dSetId + w0 : (const int*)nullptr,      \
+                e_stride, a_stride, fuse))
             switch (h->bdFB + (h->bdAugIn ? 1 : 0)) {
                 case 8: BD_LAUNCH(8, false); break;
                 case 9: BD_LAUNCH(8, true); break;
@@ -1258,9 +1278,8 @@ static int run_block_direct(bi_handle h, const double* dTheta, long long W, doub
             }
 #undef BD_LAUNCH
             if (!fuse_now)
-                block_combine_kernel<<<(unsigned)((wb + 127) / 128), 128, 0, s>>>(nB, wb, h->d, dTheta + w0 * h->d, h->dMin, h->dMax,
-                                                                                  h->dBdPart, h->dBdBad, dLogp + w0,
-                                                                                  dInfo ? dInfo + w0 : nullptr);
+                CK(launch_k(h->pdl, block_combine_kernel, dim3((unsigned)((wb + 127) / 128)), dim3(128), 0, s, nB, wb, h->d,
+                            dTheta + w0 * h->d, h->dMin, h->dMax, h->dBdPart, h->dBdBad, dLogp + w0, dInfo ? dInfo + w0 : (int*)nullptr));
         }
         h->launches += fuse_now ? 1 : 2;
         CK(cudaGetLastError());
@@ -1415,7 +1434,8 @@ int bi_stretch_propose(bi_handle h, const double* coords, const int32_t* s_idx, 
     if (ns == 0) return 0;
     CK(cudaSetDevice(h->device));
     const long long n = (long long)ns * h->d;
-    stretch_propose_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(coords, s_idx, c_idx, zz, ns, h->d, q_out);
+    CK(launch_k(h->pdl, stretch_propose_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, (cudaStream_t)stream, coords, s_idx, c_idx,
+                zz, (long long)ns, h->d, q_out));
     h->launches++;
     CK(cudaGetLastError());
     return 0;
@@ -1428,8 +1448,8 @@ int bi_stretch_accept(bi_handle h, double* coords, double* logp, const int32_t* 
         return fail(h, BI_E_ARG, "bad argument");
     if (ns == 0) return 0;
     CK(cudaSetDevice(h->device));
-    stretch_accept_kernel<<<(unsigned)((ns + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
-        coords, logp, s_idx, q, new_lp, factors, logu, ns, h->d, reinterpret_cast<long long*>(n_accepted), nan_flag);
+    CK(launch_k(h->pdl, stretch_accept_kernel, dim3((unsigned)((ns + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, coords, logp, s_idx, q,
+                new_lp, factors, logu, (long long)ns, h->d, reinterpret_cast<long long*>(n_accepted), nan_flag));
     h->launches++;
     CK(cudaGetLastError());
     return 0;

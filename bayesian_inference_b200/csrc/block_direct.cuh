@@ -127,6 +127,8 @@ __global__ void __launch_bounds__(BD_THREADS, FB <= 16 ? 4 : (FB <= 24 ? 3 : 2))
     }
     for (int idx = lane; idx < (FB + 1) * LDC; idx += 32) sC[idx] = 0.0;   // tiles above the diagonal are never written
     __syncthreads();
+    pdl_wait();        // T_b, A_b, e_b above are theta independent and older than the previous kernel (K1+K2: m, v)
+    pdl_trigger();
 
     const bool is_aug = lane == AL;
     const int nks = (P + 3) >> 2;
@@ -281,6 +283,8 @@ __global__ void __launch_bounds__(128) block_combine_kernel(int nB, long long W,
                                                             const double* __restrict__ lo, const double* __restrict__ hi,
                                                             const double* __restrict__ part, const int* __restrict__ bad_in,
                                                             double* __restrict__ logp, int* __restrict__ info) {
+    pdl_wait();
+    pdl_trigger();
     const long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= W) return;
     bool inside = true;

@@ -41,6 +41,15 @@ __device__ __forceinline__ void st_cg(double* p, double v) {
 
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
+// Programmatic dependent launch (the kernels of a sampler half-step, bi_api.cu launch_k): a kernel launched with the
+// programmatic-serialisation attribute may START before the previous kernel of the stream has finished.  pdl_wait() returns
+// when that kernel has completed and its writes are visible: everything a kernel reads that another kernel of the stream may
+// have written, and every global write, comes after it.  pdl_trigger() lets the NEXT kernel start; it is always issued after
+// pdl_wait(), so a kernel that runs ahead can only ever overlap its direct predecessor, never an older kernel.  Both are
+// no-ops for a kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // offset of element (r, c) of a 32 x (4*nks) tile stored operand-fragment-major
 __host__ __device__ __forceinline__ int of_index(int r, int c, int nks) {
     return (((r >> 3) * nks + (c >> 2)) << 5) + ((r & 7) << 2) + (c & 3);

@@ -14,12 +14,16 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "common.cuh"
+
 namespace bi {
 
 // one thread per (proposal k, parameter) element; s_idx[k] = walker being moved, c_idx[k] = its partner
 __global__ void stretch_propose_kernel(const double* __restrict__ coords, const int* __restrict__ s_idx,
                                        const int* __restrict__ c_idx, const double* __restrict__ zz, long long ns, int d,
                                        double* __restrict__ q) {
+    pdl_wait();
+    pdl_trigger();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= ns * d) return;
     const long long k = idx / d;
@@ -35,6 +39,8 @@ __global__ void stretch_accept_kernel(double* __restrict__ coords, double* __res
                                       const double* __restrict__ q, const double* __restrict__ new_lp,
                                       const double* __restrict__ factors, const double* __restrict__ logu, long long ns,
                                       int d, long long* __restrict__ n_accepted, int* __restrict__ nan_flag) {
+    pdl_wait();
+    pdl_trigger();
     const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= ns) return;
     const double nl = new_lp[k];

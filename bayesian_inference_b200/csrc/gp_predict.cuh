@@ -500,7 +500,9 @@ __device__ __forceinline__ void gp_predict_unit(unsigned char* smem_raw, const P
     long long t0_ = clock64();
 #endif
 
-    for (int idx = tid; idx < d * N; idx += GP_THREADS) sX[idx] = __ldg(pc.XsT + idx);
+    for (int idx = tid; idx < d * N; idx += GP_THREADS) sX[idx] = __ldg(pc.XsT + idx);   // the image: never written after bi_create
+    pdl_wait();        // theta may come from the previous kernel of the stream (the proposals of a sampler half-step)
+    pdl_trigger();
     for (int idx = tid; idx < GP_WT * d; idx += GP_THREADS) {
         const int wl = idx / d, k = idx - wl * d;
         const long long w = w0 + wl;
