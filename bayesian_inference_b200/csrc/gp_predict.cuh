@@ -47,7 +47,8 @@ constexpr int GP_WT_MAX = 64;
 // A third instantiation, 8 walkers per CTA (256 threads, 32 per walker in K1, one 8-row fragment per warp in K2), is the
 // LATENCY configuration for small batches (the W/2 proposals of a sampler half-step): it spreads 50 walkers x 30 PCs over
 // 210 CTAs instead of 60, and a CTA's K1 + K2 take a quarter of the time.  Same arithmetic per element and the same
-// summation order, hence bit-identical (m, v).
+// summation order, hence bit-identical (m, v).  A fourth width, 16 walkers (256 threads, 16 per walker in K1, two m-fragments per
+// warp in K2), exists only inside gp_predict_mixed_kernel below: the tiles of a partly empty last wave.
 __host__ __device__ constexpr int gp_threads(int wt) { return wt >= 32 ? wt * 8 : 256; }
 
 __host__ __device__ inline size_t gp_smem_bytes(int d, int Nmax, int GP_WT) {
