@@ -27,7 +27,7 @@ EXPORTS = [
     "bi_stretch_propose", "bi_stretch_accept", "bi_set_data_sets", "bi_log_posterior_sets", "bi_stretch_randoms_philox",
     "bi_trainer_create", "bi_trainer_lml", "bi_trainer_lml_host", "bi_trainer_factor", "bi_trainer_factor_host",
     "bi_trainer_destroy", "bi_trainer_last_error", "bi_trainer_launches",
-    "bi_loglikelihood_noalloc",
+    "bi_loglikelihood_noalloc", "bi_stretch_accept_record",
 ]
 
 # entry points that return an int status (0 ok, <0 bad argument, >0 CUDA error code); named one by one so that adding
@@ -38,7 +38,7 @@ INT_STATUS_EXPORTS = [
     "bi_log_posterior", "bi_log_posterior_host", "bi_loglikelihood_host",
     "bi_stretch_propose", "bi_stretch_accept", "bi_set_data_sets", "bi_log_posterior_sets", "bi_stretch_randoms_philox",
     "bi_trainer_create", "bi_trainer_lml", "bi_trainer_lml_host", "bi_trainer_factor", "bi_trainer_factor_host",
-    "bi_loglikelihood_noalloc",
+    "bi_loglikelihood_noalloc", "bi_stretch_accept_record",
 ]
 
 MODE = {"dense": 0, "structured": 1, "woodbury": 2}
@@ -143,6 +143,7 @@ def load() -> C.CDLL:
     lib.bi_loglikelihood_host.argtypes = [h, dp, dp, i64, C.c_int32, dp, dp]
     lib.bi_stretch_propose.argtypes = [h, dp, dp, dp, dp, i64, dp, C.c_void_p]
     lib.bi_stretch_accept.argtypes = [h, dp, dp, dp, dp, dp, dp, dp, i64, dp, dp, C.c_void_p]
+    lib.bi_stretch_accept_record.argtypes = [h, dp, dp, dp, dp, dp, dp, dp, i64, dp, dp, dp, dp, dp, C.c_void_p]
     lib.bi_set_data_sets.argtypes = [h, C.c_int32, dp, dp]
     lib.bi_log_posterior_sets.argtypes = [h, dp, dp, i64, C.c_double, C.c_int, dp, dp, C.c_void_p]
     i32 = C.c_int32

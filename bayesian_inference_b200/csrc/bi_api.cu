@@ -1449,7 +1449,24 @@ int bi_stretch_accept(bi_handle h, double* coords, double* logp, const int32_t* 
     if (ns == 0) return 0;
     CK(cudaSetDevice(h->device));
     CK(launch_k(h->pdl, stretch_accept_kernel, dim3((unsigned)((ns + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, coords, logp, s_idx, q,
-                new_lp, factors, logu, (long long)ns, h->d, reinterpret_cast<long long*>(n_accepted), nan_flag));
+                new_lp, factors, logu, (long long)ns, h->d, reinterpret_cast<long long*>(n_accepted), nan_flag, (const int*)nullptr,
+                (double*)nullptr, (double*)nullptr));
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int bi_stretch_accept_record(bi_handle h, double* coords, double* logp, const int32_t* s_idx, const double* q, const double* new_lp,
+                             const double* factors, const double* logu, int64_t ns, int64_t* n_accepted, int32_t* nan_flag,
+                             const int32_t* other_idx, double* chain_out, double* lp_out, void* stream) {
+    if (!h || !coords || !logp || !s_idx || !q || !new_lp || !factors || !logu || !n_accepted || !nan_flag || !other_idx ||
+        !chain_out || !lp_out || ns < 0)
+        return fail(h, BI_E_ARG, "bad argument");
+    if (ns == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    CK(launch_k(h->pdl, stretch_accept_kernel, dim3((unsigned)((ns + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, coords, logp, s_idx, q,
+                new_lp, factors, logu, (long long)ns, h->d, reinterpret_cast<long long*>(n_accepted), nan_flag, other_idx, chain_out,
+                lp_out));
     h->launches++;
     CK(cudaGetLastError());
     return 0;

@@ -34,11 +34,16 @@ __global__ void stretch_propose_kernel(const double* __restrict__ coords, const 
     q[idx] = __dsub_rn(c, __dmul_rn(__dsub_rn(c, s), zz[k]));
 }
 
-// one thread per proposal; walkers of one half-step are distinct, so the scatter needs no atomics
+// one thread per proposal; walkers of one half-step are distinct, so the scatter needs no atomics.
+// chain_out != nullptr (the second half-step of a step): the state of the ensemble after this step is recorded as well --
+// thread k writes the row of its own walker after its accept decision and the row of other_idx[k], a walker of the half
+// that does not move in this half-step (other_idx = the s_idx of the first half-step: together they are all W walkers).
 __global__ void stretch_accept_kernel(double* __restrict__ coords, double* __restrict__ logp, const int* __restrict__ s_idx,
                                       const double* __restrict__ q, const double* __restrict__ new_lp,
                                       const double* __restrict__ factors, const double* __restrict__ logu, long long ns,
-                                      int d, long long* __restrict__ n_accepted, int* __restrict__ nan_flag) {
+                                      int d, long long* __restrict__ n_accepted, int* __restrict__ nan_flag,
+                                      const int* __restrict__ other_idx, double* __restrict__ chain_out,
+                                      double* __restrict__ lp_out) {
     pdl_wait();
     pdl_trigger();
     const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -55,6 +60,15 @@ __global__ void stretch_accept_kernel(double* __restrict__ coords, double* __res
         for (int p = 0; p < d; ++p) coords[(long long)w * d + p] = q[k * d + p];
         logp[w] = nl;
         n_accepted[w] += 1;
+    }
+    if (chain_out != nullptr) {
+        const int o = other_idx[k];
+        for (int p = 0; p < d; ++p) {
+            chain_out[(long long)w * d + p] = coords[(long long)w * d + p];
+            chain_out[(long long)o * d + p] = coords[(long long)o * d + p];
+        }
+        lp_out[w] = logp[w];
+        lp_out[o] = logp[o];
     }
 }
 

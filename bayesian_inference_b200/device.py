@@ -293,11 +293,22 @@ class DeviceEmulator:
                                                  C.c_void_p(c_idx.data_ptr()), C.c_void_p(zz.data_ptr()), int(s_idx.shape[0]),
                                                  C.c_void_p(q_out.data_ptr()), C.c_void_p(stream)), "bi_stretch_propose")
 
-    def stretch_accept(self, coords, logp, s_idx, q, new_lp, factors, logu, n_accepted, nan_flag) -> None:
-        """Accept/reject one half-step in place (coords, logp, n_accepted int64 (W), nan_flag int32 (1))."""
+    def stretch_accept(self, coords, logp, s_idx, q, new_lp, factors, logu, n_accepted, nan_flag, record=None) -> None:
+        """Accept/reject one half-step in place (coords, logp, n_accepted int64 (W), nan_flag int32 (1)).
+        record = (other_idx int32 (ns), chain_out f64 (W, d), lp_out f64 (W)): also store the ensemble after the step
+        (second half-step of a step; other_idx = the walkers of the first half): bi_stretch_accept_record."""
         import torch
 
         stream = torch.cuda.current_stream(coords.device).cuda_stream
+        if record is not None:
+            other_idx, chain_out, lp_out = record
+            self._check(self._lib.bi_stretch_accept_record(
+                self._h, C.c_void_p(coords.data_ptr()), C.c_void_p(logp.data_ptr()), C.c_void_p(s_idx.data_ptr()),
+                C.c_void_p(q.data_ptr()), C.c_void_p(new_lp.data_ptr()), C.c_void_p(factors.data_ptr()),
+                C.c_void_p(logu.data_ptr()), int(s_idx.shape[0]), C.c_void_p(n_accepted.data_ptr()),
+                C.c_void_p(nan_flag.data_ptr()), C.c_void_p(other_idx.data_ptr()), C.c_void_p(chain_out.data_ptr()),
+                C.c_void_p(lp_out.data_ptr()), C.c_void_p(stream)), "bi_stretch_accept_record")
+            return
         self._check(self._lib.bi_stretch_accept(self._h, C.c_void_p(coords.data_ptr()), C.c_void_p(logp.data_ptr()),
                                                 C.c_void_p(s_idx.data_ptr()), C.c_void_p(q.data_ptr()),
                                                 C.c_void_p(new_lp.data_ptr()), C.c_void_p(factors.data_ptr()),

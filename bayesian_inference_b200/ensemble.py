@@ -22,6 +22,8 @@ re-implementation in tests/test_ensemble.py, and the GPU-vs-oracle chain identit
 """
 from __future__ import annotations
 
+import os
+
 from typing import Callable, Optional
 
 import numpy as np
@@ -244,6 +246,9 @@ class DeviceStretchEnsemble(StretchEnsemble):
             raise ValueError(f"ndim {ndim} does not match the emulator's parameter dimension {device_emulator.d}")
         self.graph = bool(graph)
         self.n_graph_replays = 0
+        # the ensemble after each step is stored by the accept of its second half-step (bi_stretch_accept_record) instead of
+        # two device-to-device copies per step; needs the two halves to be of equal size (developer knob BI_RECORD_FUSE=0)
+        self._record_fused = nwalkers % 2 == 0 and os.environ.get("BI_RECORD_FUSE", "1") != "0"
         self._buf = None           # state, scratch and (with graph=True) the captured block live as long as the sampler
         self.world, self.rank = 1, 0
         try:
@@ -298,15 +303,19 @@ class DeviceStretchEnsemble(StretchEnsemble):
     def _run_block(self, nb: int) -> None:
         bf = self._buf
         coords, logp, q, new_lp, n_acc, nan_flag, rd = (bf[k] for k in ("coords", "logp", "q", "new_lp", "n_acc", "nan_flag", "rd"))
+        fused = self._record_fused
         for t in range(nb):
             for split in range(2):
                 s_idx = rd["s_idx"][t, split]
                 self.dev.stretch_propose(coords, s_idx, rd["c_idx"][t, split], rd["zz"][t, split], q)
                 self._device_log_prob(q, new_lp)
+                # the accept of the second half also stores the ensemble after the step (no copies between the steps)
+                record = (rd["s_idx"][t, 0], bf["chain_b"][t], bf["lp_b"][t]) if (fused and split == 1) else None
                 self.dev.stretch_accept(coords, logp, s_idx, q, new_lp, rd["factors"][t, split], rd["logu"][t, split],
-                                        n_acc, nan_flag)
-            bf["chain_b"][t].copy_(coords)
-            bf["lp_b"][t].copy_(logp)
+                                        n_acc, nan_flag, record=record)
+            if not fused:
+                bf["chain_b"][t].copy_(coords)
+                bf["lp_b"][t].copy_(logp)
 
     def _capture(self, device) -> None:
         """Capture ``block`` steps as one CUDA graph.  Every kernel of the block (and the communicator) has already run once

@@ -190,6 +190,14 @@ int bi_stretch_propose(bi_handle h, const double* coords, const int32_t* s_idx, 
 int bi_stretch_accept(bi_handle h, double* coords, double* logp, const int32_t* s_idx, const double* q,
                       const double* new_lp, const double* factors, const double* logu, int64_t ns,
                       int64_t* n_accepted, int32_t* nan_flag, void* stream);
+/* bi_stretch_accept_record: the accept of the SECOND half-step of a step, which also stores the ensemble after the step the
+ * way emcee's backend keeps every iteration (the chain and log_prob mcmc.py:111-116 reads back): chain_out (W, d) and
+ * lp_out (W) receive the rows of the ns walkers moved here (after their accept decision) and of the ns walkers named by
+ * other_idx (the s_idx of the first half-step, unchanged in this one); W = 2 ns.  Otherwise identical to bi_stretch_accept. */
+int bi_stretch_accept_record(bi_handle h, double* coords, double* logp, const int32_t* s_idx, const double* q,
+                             const double* new_lp, const double* factors, const double* logu, int64_t ns,
+                             int64_t* n_accepted, int32_t* nan_flag, const int32_t* other_idx, double* chain_out,
+                             double* lp_out, void* stream);
 
 /* bi_stretch_randoms_philox: the chain-independent numbers of `nsteps` steps generated ON the device (Philox4x32-10,
  * counter = (proposal, half, step), key = seed), shaped (nsteps, 2, n_half) like the host-drawn arrays the two calls
