@@ -128,6 +128,44 @@ def test_emcee_stream_sampler_as_cuda_graph_is_the_same_chain():
     assert g2.n_graph_replays == 4 and np.array_equal(g2.get_chain(), host.get_chain()[:128])
 
 
+def test_accept_record_equals_accept_followed_by_copies():
+    """bi_stretch_accept_record (the accept of a step's second half-step, which also stores the ensemble) against
+    bi_stretch_accept followed by copies of the state -- the same coords, logp, counts and the same record, bit for bit."""
+    import torch
+
+    from bayesian_inference_b200.device import DeviceEmulator
+
+    z, _ = load_golden("mid")
+    d, W = int(z["d"]), 48
+    ns = W // 2
+    rng = np.random.default_rng(11)
+    perm = rng.permutation(W).astype(np.int32)
+    first, second = np.sort(perm[:ns]), np.sort(perm[ns:])
+    with DeviceEmulator(image.EmulatorImage.from_flat(z)) as dev:
+        dv = torch.device("cuda", dev.device)
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dv)       # noqa: E731
+        coords0, logp0 = rng.uniform(0.2, 0.8, (W, d)), rng.normal(-50.0, 5.0, W)
+        q, new_lp = rng.uniform(0.2, 0.8, (ns, d)), rng.normal(-50.0, 5.0, ns)
+        factors, logu = rng.normal(0.0, 1.0, ns), np.log(rng.uniform(size=ns))
+        out = []
+        for record in (False, True):
+            coords, logp = t(coords0), t(logp0)
+            n_acc = torch.zeros(W, dtype=torch.int64, device=dv)
+            nan_flag = torch.zeros(1, dtype=torch.int32, device=dv)
+            chain = torch.full((W, d), float("nan"), dtype=torch.float64, device=dv)
+            lp = torch.full((W,), float("nan"), dtype=torch.float64, device=dv)
+            rec = (t(first), chain, lp) if record else None
+            dev.stretch_accept(coords, logp, t(second), t(q), t(new_lp), t(factors), t(logu), n_acc, nan_flag, record=rec)
+            if not record:
+                chain.copy_(coords)
+                lp.copy_(logp)
+            torch.cuda.synchronize(dv)
+            out.append([x.cpu().numpy() for x in (coords, logp, n_acc, chain, lp)])
+    for a, b in zip(*out):
+        assert np.array_equal(a, b)
+    assert 0 < out[0][2].sum() < ns and not np.isnan(out[1][3]).any()        # some accepted, some not; every row recorded
+
+
 def test_device_sampler_raises_on_nan_like_emcee():
     """A covariance that is not positive definite gives NaN; emcee raises ValueError, so does the device sampler."""
     from bayesian_inference_b200.device import DeviceEmulator
